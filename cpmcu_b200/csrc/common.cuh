@@ -1,0 +1,269 @@
+// Shared device helpers for the sm_100a W4A16 kernels: mbarrier / TMA / PDL PTX wrappers, the
+// legacy-path MMA used in the HBM-bound regime, and THE dequantisation routine (one definition,
+// used by every kernel and by the dequant dump, so "bit-exact dequant" is one piece of code).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------
+// small PTX wrappers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+
+// L2 eviction-priority policies for TMA loads (createpolicy encodings)
+static constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
+static constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
+static constexpr uint64_t kEvictLast = 0x14F0000000000000ull;
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1, uint64_t hint) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "l"(hint)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1, int c2, uint64_t hint) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(hint)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+
+// programmatic dependent launch: no-ops unless the launch carried the attribute
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait_prior_grids() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+template <int lut>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm volatile("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(lut));
+  return r;
+}
+
+__device__ __forceinline__ void ldmatrix_x2(uint32_t& r0, uint32_t& r1, uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];"
+               : "=r"(r0), "=r"(r1)
+               : "r"(addr));
+}
+__device__ __forceinline__ void ldmatrix_x4(uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3,
+                                            uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(addr));
+}
+
+// ---------------------------------------------------------------------------------------------
+// element-type traits
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+struct Elem;
+template <>
+struct Elem<__half> {
+  using T2 = __half2;
+  static constexpr CUtensorMapDataType kTmaType = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  static __device__ __forceinline__ __half from_float(float f) { return __float2half_rn(f); }
+  static __device__ __forceinline__ float to_float(__half h) { return __half2float(h); }
+};
+template <>
+struct Elem<__nv_bfloat16> {
+  using T2 = __nv_bfloat162;
+  static constexpr CUtensorMapDataType kTmaType = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  static __device__ __forceinline__ __nv_bfloat16 from_float(float f) {
+    return __float2bfloat16_rn(f);
+  }
+  static __device__ __forceinline__ float to_float(__nv_bfloat16 h) {
+    return __bfloat162float(h);
+  }
+};
+
+// D(16x8,f32) += A(16x16,T,row) * B(16x8,T,col): the register-operand tensor path.  In the
+// HBM-bound regime the weights arrive as registers straight out of the dequantiser, which is the
+// one case where mma.sync (not tcgen05, whose operands live in shared/tensor memory) is the right
+// instruction on sm_100a: a round trip through shared memory would cost 4x the bytes of the int4
+// stream (DESIGN.md "Why mma.sync below the ridge").
+template <typename T>
+__device__ __forceinline__ void mma_m16n8k16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                             uint32_t b1);
+template <>
+__device__ __forceinline__ void mma_m16n8k16<__half>(float (&d)[4], const uint32_t (&a)[4],
+                                                     uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+      "{%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <>
+__device__ __forceinline__ void mma_m16n8k16<__nv_bfloat16>(float (&d)[4], const uint32_t (&a)[4],
+                                                            uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+      "{%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// ---------------------------------------------------------------------------------------------
+// dequantisation (the reference's device semantics: marlin_device_ops.cuh:91-137 for the exact
+// integer -> float step, :294-303 for the single-rounding group-scale multiply)
+//
+// One 32-bit word of the Marlin stream holds, for lane (g = lane/4, t = lane%4) and 16-column
+// tile j, the eight uint4b8 nibbles of rows k in {2t, 2t+1, 2t+8, 2t+9} x cols n in {g, g+8}:
+//     nibble:   0        1        2        3        4        5        6        7
+//     (k, n): (2t,g) (2t+8,g) (2t,g+8) (2t+8,g+8) (2t+1,g) (2t+9,g) (2t+1,g+8) (2t+9,g+8)
+// dequant_word() returns them as the four 32-bit registers of a 16(n) x 16(k) row-major
+// m16n8k16 A-operand fragment (weights as the M side, tokens as the N side):
+//     w[0] = {W[2t  ][g  ], W[2t+1][g  ]}      w[1] = {W[2t  ][g+8], W[2t+1][g+8]}
+//     w[2] = {W[2t+8][g  ], W[2t+9][g  ]}      w[3] = {W[2t+8][g+8], W[2t+9][g+8]}
+// Integer step: the nibble is OR-ed into the mantissa of a magic constant (1024+q for fp16,
+// 128+q for bf16) and the bias (+8 zero point) removed by one exact subtraction / FMA; every
+// value q-8 in [-8, 7] is exact, so any correct method is bit-identical to the reference's.
+// Scale step (SCALED): one multiply in T with round-to-nearest-even — the only rounding on the
+// weight path and the reference's rounding point (HMUL2).
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+struct Dequant;
+
+template <>
+struct Dequant<__half> {
+  // s_lo / s_hi: the group scale of column g / g+8, broadcast to both halves
+  template <bool SCALED>
+  static __device__ __forceinline__ void word(uint32_t q, uint32_t s_lo, uint32_t s_hi,
+                                              uint32_t (&w)[4]) {
+    constexpr uint32_t LO = 0x000f000f, HI = 0x00f000f0, EX = 0x64006400;
+    constexpr uint32_t SUB = 0x64086408;  // 1032 = 1024 + 8
+    constexpr uint32_t MUL = 0x2c002c00;  // 1/16
+    constexpr uint32_t ADD = 0xd480d480;  // -72 = -(1024/16 + 8)
+    const uint32_t q8 = q >> 8;
+    uint32_t lo0 = lop3<(0xf0 & 0xcc) | 0xaa>(q, LO, EX);
+    uint32_t hi0 = lop3<(0xf0 & 0xcc) | 0xaa>(q, HI, EX);
+    uint32_t lo1 = lop3<(0xf0 & 0xcc) | 0xaa>(q8, LO, EX);
+    uint32_t hi1 = lop3<(0xf0 & 0xcc) | 0xaa>(q8, HI, EX);
+    __half2 v0 = __hsub2(as_h2(lo0), as_h2(SUB));
+    __half2 v2 = __hfma2(as_h2(hi0), as_h2(MUL), as_h2(ADD));
+    __half2 v1 = __hsub2(as_h2(lo1), as_h2(SUB));
+    __half2 v3 = __hfma2(as_h2(hi1), as_h2(MUL), as_h2(ADD));
+    if (SCALED) {
+      v0 = __hmul2(v0, as_h2(s_lo));
+      v2 = __hmul2(v2, as_h2(s_lo));
+      v1 = __hmul2(v1, as_h2(s_hi));
+      v3 = __hmul2(v3, as_h2(s_hi));
+    }
+    w[0] = as_u32(v0);
+    w[1] = as_u32(v1);
+    w[2] = as_u32(v2);
+    w[3] = as_u32(v3);
+  }
+  static __device__ __forceinline__ __half2 as_h2(uint32_t u) {
+    return *reinterpret_cast<__half2*>(&u);
+  }
+  static __device__ __forceinline__ uint32_t as_u32(__half2 h) {
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+};
+
+template <>
+struct Dequant<__nv_bfloat16> {
+  template <bool SCALED>
+  static __device__ __forceinline__ void word(uint32_t q, uint32_t s_lo, uint32_t s_hi,
+                                              uint32_t (&w)[4]) {
+    constexpr uint32_t MASK = 0x000f000f, EX = 0x43004300;  // 128 + q, ulp(128) = 1
+    constexpr uint32_t ONE = 0x3f803f80;                    // 1.0
+    constexpr uint32_t ADD = 0xc308c308;                    // -136 = -(128 + 8)
+    uint32_t lo0 = lop3<(0xf0 & 0xcc) | 0xaa>(q, MASK, EX);
+    uint32_t hi0 = lop3<(0xf0 & 0xcc) | 0xaa>(q >> 4, MASK, EX);
+    uint32_t lo1 = lop3<(0xf0 & 0xcc) | 0xaa>(q >> 8, MASK, EX);
+    uint32_t hi1 = lop3<(0xf0 & 0xcc) | 0xaa>(q >> 12, MASK, EX);
+    __nv_bfloat162 v0 = __hfma2(as_b2(lo0), as_b2(ONE), as_b2(ADD));
+    __nv_bfloat162 v2 = __hfma2(as_b2(hi0), as_b2(ONE), as_b2(ADD));
+    __nv_bfloat162 v1 = __hfma2(as_b2(lo1), as_b2(ONE), as_b2(ADD));
+    __nv_bfloat162 v3 = __hfma2(as_b2(hi1), as_b2(ONE), as_b2(ADD));
+    if (SCALED) {
+      v0 = __hmul2(v0, as_b2(s_lo));
+      v2 = __hmul2(v2, as_b2(s_lo));
+      v1 = __hmul2(v1, as_b2(s_hi));
+      v3 = __hmul2(v3, as_b2(s_hi));
+    }
+    w[0] = as_u32(v0);
+    w[1] = as_u32(v1);
+    w[2] = as_u32(v2);
+    w[3] = as_u32(v3);
+  }
+  static __device__ __forceinline__ __nv_bfloat162 as_b2(uint32_t u) {
+    return *reinterpret_cast<__nv_bfloat162*>(&u);
+  }
+  static __device__ __forceinline__ uint32_t as_u32(__nv_bfloat162 h) {
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+};
+
+// A lane's 16 bytes of a 64-column scale chunk are 8 scales for columns g + 8*jj, jj = 0..7
+// (gptq2marlin.py:55-57), i.e. word j = {s[16j+g], s[16j+g+8]}.  Split a word into the two
+// broadcast pairs dequant_word wants.
+__device__ __forceinline__ void broadcast_scale_pair(uint32_t s, uint32_t& s_lo, uint32_t& s_hi) {
+  s_lo = __byte_perm(s, 0, 0x1010);
+  s_hi = __byte_perm(s, 0, 0x3232);
+}
+
+// inverse of SCALE_PERM_SINGLE (gptq2marlin.py:58-60): position of column (n % 32) inside its
+// 32-column block of a channelwise (group_size == -1) scale row
+__device__ __forceinline__ int chan_scale_pos(int n) {
+  const int c = n & 31;
+  // SCALE_PERM_SINGLE[8*i + jj] = 2*i + {0,1,8,9,16,17,24,25}[jj]
+  const int i = (c & 7) >> 1;
+  const int jj = ((c >> 3) << 1) | (c & 1);
+  return (n & ~31) | (8 * i + jj);
+}
+
+}  // namespace b200

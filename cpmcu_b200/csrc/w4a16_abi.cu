@@ -1,0 +1,490 @@
+// C ABI + host-side dispatch of libb200_w4a16.so (see include/b200_w4a16.h).
+//
+// Host logic mirrors what the reference does on the host for this path
+// (gptq_marlin.cu:42-86 validation, gptq_marlin_mm.cu:34-207 configuration + M loop) but for the
+// sm_100a kernels: it validates, picks a kernel configuration from the shape, encodes (and caches)
+// the TMA descriptors, and launches on the caller's stream.  No allocation, no host<->device sync,
+// graph-capturable.
+#include "../../include/b200_w4a16.h"
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+
+#include "aux_kernels.cuh"
+#include "decode_kernel.cuh"
+#include "host_common.h"
+
+namespace b200 {
+
+thread_local std::string g_last_error;
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  // like the reference's VALUE_CHECK / ERROR_CHECK (src/utils.cuh:54-66) the message also goes to stderr
+  fprintf(stderr, "b200_w4a16 %s: %s\n", code == B200_W4A16_EINVAL ? "value error" : "error", buf);
+  return code;
+}
+
+// ------------------------------------------------------------------------------------------
+// device properties (cached) and the driver entry point for descriptor encoding
+// ------------------------------------------------------------------------------------------
+int sm_count() {
+  static int sms = [] {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) {
+      (void)cudaGetLastError();
+      return 148;  // B200; only reached by the sizing helpers on a machine without a device
+    }
+    return v;
+  }();
+  return sms;
+}
+
+using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                              const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                              CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                              CUtensorMapFloatOOBfill);
+EncodeFn encode_fn() {
+  static EncodeFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeFn>(p);
+  }();
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr;
+  uint64_t d0, d1, d2, s1, s2;
+  uint32_t b0, b1, b2, misc;
+  bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < sizeof(MapKey) / 8; ++i) h = (h ^ w[i]) * 1099511628211ull;
+    return static_cast<size_t>(h);
+  }
+};
+std::mutex g_map_mu;
+std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
+
+// rank 2 or 3 tiled descriptor; dims/strides innermost first (strides[] in bytes for dims 1..)
+int get_tensor_map(CUtensorMap* out, const void* ptr, CUtensorMapDataType type, int rank,
+                   const uint64_t* dims, const uint64_t* strides, const uint32_t* box,
+                   CUtensorMapSwizzle swz) {
+  MapKey key;
+  std::memset(&key, 0, sizeof(key));
+  key.ptr = ptr;
+  key.d0 = dims[0];
+  key.d1 = dims[1];
+  key.d2 = rank > 2 ? dims[2] : 0;
+  key.s1 = strides[0];
+  key.s2 = rank > 2 ? strides[1] : 0;
+  key.b0 = box[0];
+  key.b1 = box[1];
+  key.b2 = rank > 2 ? box[2] : 0;
+  key.misc = (static_cast<uint32_t>(type) << 8) | (static_cast<uint32_t>(swz) << 4) | rank;
+  {
+    std::lock_guard<std::mutex> lk(g_map_mu);
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  EncodeFn enc = encode_fn();
+  if (!enc) return fail(B200_W4A16_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t gdim[3] = {dims[0], dims[1], rank > 2 ? dims[2] : 1};
+  cuuint64_t gstr[2] = {strides[0], rank > 2 ? strides[1] : 0};
+  cuuint32_t bx[3] = {box[0], box[1], rank > 2 ? box[2] : 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, type, rank, const_cast<void*>(ptr), gdim, gstr, bx, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(B200_W4A16_ECUDA,
+                "cuTensorMapEncodeTiled failed (%d): ptr=%p rank=%d dims=[%llu,%llu,%llu] "
+                "strides=[%llu,%llu] box=[%u,%u,%u]",
+                static_cast<int>(r), ptr, rank, (unsigned long long)gdim[0],
+                (unsigned long long)gdim[1], (unsigned long long)gdim[2], (unsigned long long)gstr[0],
+                (unsigned long long)gstr[1], bx[0], bx[1], bx[2]);
+  std::lock_guard<std::mutex> lk(g_map_mu);
+  if (g_maps.size() > 65536) g_maps.clear();
+  g_maps.emplace(key, *out);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// decode-regime configurations
+// ------------------------------------------------------------------------------------------
+struct GemmCall {
+  const void* a;
+  const int32_t* qweight;
+  const void* scales;
+  int32_t* workspace;
+  void* c;
+  float* c_tmp;
+  const void* bias;
+  const void* residual;
+  int m, n, k;       // m <= 8 * nt of the configuration
+  int group_size;
+  bool pdl;
+  cudaStream_t stream;
+};
+
+struct DecodeConfig {
+  const char* name;
+  int nt, chunks, krows, warps, stages;
+  bool grouped;
+  int dtype;
+  int (*launch)(const GemmCall&);
+  int smem;
+};
+
+template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED>
+int launch_decode(const GemmCall& g) {
+  using Cfg = DecodeCfg<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>;
+  auto kern = w4a16_decode_kernel<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>;
+  static bool attr_set = false;  // benign race: idempotent
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess)
+      return fail(B200_W4A16_ECUDA, "cudaFuncSetAttribute(smem=%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+    attr_set = true;
+  }
+  CUtensorMap tm_w, tm_s, tm_a;
+  {  // weights: int32 [K/16][N/64][128]
+    const uint64_t dims[3] = {128, static_cast<uint64_t>(g.n / 64), static_cast<uint64_t>(g.k / 16)};
+    const uint64_t strides[2] = {512, static_cast<uint64_t>(g.n) * 8};
+    const uint32_t box[3] = {128, CHUNKS, KROWS};
+    if (int rc = get_tensor_map(&tm_w, g.qweight, CU_TENSOR_MAP_DATA_TYPE_INT32, 3, dims, strides, box,
+                                CU_TENSOR_MAP_SWIZZLE_NONE))
+      return rc;
+  }
+  if (GROUPED) {  // scales: T [K/128][N/64][64]
+    const uint64_t dims[3] = {64, static_cast<uint64_t>(g.n / 64), static_cast<uint64_t>(g.k / 128)};
+    const uint64_t strides[2] = {128, static_cast<uint64_t>(g.n) * 2};
+    const uint32_t box[3] = {64, CHUNKS, 1};
+    if (int rc = get_tensor_map(&tm_s, g.scales, Elem<T>::kTmaType, 3, dims, strides, box,
+                                CU_TENSOR_MAP_SWIZZLE_NONE))
+      return rc;
+  } else {
+    tm_s = tm_w;
+  }
+  {  // activations: T [M][K], 64-wide (128-byte) boxes, 128B swizzle, rows past M zero-filled
+    const uint64_t dims[2] = {static_cast<uint64_t>(g.k), static_cast<uint64_t>(g.m)};
+    const uint64_t strides[1] = {static_cast<uint64_t>(g.k) * 2};
+    const uint32_t box[2] = {64, NT * 8};
+    if (int rc = get_tensor_map(&tm_a, g.a, Elem<T>::kTmaType, 2, dims, strides, box,
+                                CU_TENSOR_MAP_SWIZZLE_128B))
+      return rc;
+  }
+  DecodeArgs args;
+  args.c = g.c;
+  args.c_tmp = g.c_tmp;
+  args.workspace = g.workspace;
+  args.scales = g.scales;
+  args.bias = g.bias;
+  args.residual = g.residual;
+  args.m = g.m;
+  args.n = g.n;
+  args.k = g.k;
+  args.ncols = (g.n + Cfg::TN - 1) / Cfg::TN;
+  args.kblks = g.k / Cfg::KB;
+  const long long units = static_cast<long long>(args.ncols) * args.kblks;
+  const int grid = static_cast<int>(units < sm_count() ? units : sm_count());
+  args.slot_max = decode_slot_max(args.kblks, units, grid);
+
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(Cfg::THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = g.stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g.pdl ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tm_w, tm_s, tm_a, args);
+  if (e != cudaSuccess) return fail(B200_W4A16_ECUDA, "decode kernel launch: %s", cudaGetErrorString(e));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return 0;
+}
+
+#define DCFG(T, DT, NT, CH, KR, WP, ST, GR)                                              \
+  {#T "/nt" #NT "/tn" #CH "x64/kb" #KR "x16/w" #WP "/s" #ST "/" #GR, NT, CH, KR, WP, ST, GR, DT, \
+   &launch_decode<T, NT, CH, KR, WP, ST, GR>, DecodeCfg<T, NT, CH, KR, WP, ST, GR>::SMEM_BYTES}
+
+// geometry families (id within family = index):  chunks, krows, warps, stages
+#define DECODE_FAMILY(T, DT, NT, GR)                                                    \
+  DCFG(T, DT, NT, 2, 8, 8, 8, GR), DCFG(T, DT, NT, 4, 8, 8, 5, GR), DCFG(T, DT, NT, 4, 4, 8, 8, GR), \
+      DCFG(T, DT, NT, 8, 4, 8, 5, GR), DCFG(T, DT, NT, 4, 8, 16, 5, GR), DCFG(T, DT, NT, 2, 8, 16, 8, GR)
+constexpr int kGeoms = 6;
+
+const DecodeConfig g_decode[] = {
+    DECODE_FAMILY(__half, 0, 1, true),          DECODE_FAMILY(__half, 0, 2, true),
+    DECODE_FAMILY(__half, 0, 4, true),          DECODE_FAMILY(__nv_bfloat16, 1, 1, true),
+    DECODE_FAMILY(__nv_bfloat16, 1, 2, true),   DECODE_FAMILY(__nv_bfloat16, 1, 4, true),
+    DECODE_FAMILY(__half, 0, 1, false),         DECODE_FAMILY(__half, 0, 2, false),
+    DECODE_FAMILY(__half, 0, 4, false),         DECODE_FAMILY(__nv_bfloat16, 1, 1, false),
+    DECODE_FAMILY(__nv_bfloat16, 1, 2, false),  DECODE_FAMILY(__nv_bfloat16, 1, 4, false),
+};
+
+// index into g_decode
+int decode_index(int dtype, int nt, bool grouped, int geom) {
+  const int nti = nt == 1 ? 0 : (nt == 2 ? 1 : 2);
+  return ((grouped ? 0 : 6) + dtype * 3 + nti) * kGeoms + geom;
+}
+
+int nt_for_m(int m) { return m <= 8 ? 1 : (m <= 16 ? 2 : 4); }
+
+// shape -> geometry.  Goal: >= ~6 units per CTA for balance, the widest tile that allows it (wide
+// tiles amortise the activation re-reads at M = 16..32), 16 warps when the token tile is small.
+int pick_geometry(int m, int n, int k) {
+  const long long sms = sm_count();
+  auto units = [&](int chunks, int krows) {
+    return static_cast<long long>((n + chunks * 64 - 1) / (chunks * 64)) * (k / (krows * 16));
+  };
+  const bool k128 = (k % 128) == 0;
+  if (k128 && n % 512 == 0 && units(8, 4) >= 12 * sms) return 3;   // tn512 kb64
+  if (k128 && units(4, 8) >= 6 * sms) return 1;                    // tn256 kb128
+  if (units(4, 4) >= 6 * sms) return 2;                            // tn256 kb64
+  if (k128) return 0;                                              // tn128 kb128
+  return 2;
+}
+
+struct Geom { int chunks, krows; };
+const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}};
+
+}  // namespace b200
+
+using namespace b200;
+
+// ------------------------------------------------------------------------------------------
+// exported functions
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* b200_w4a16_last_error(void) { return g_last_error.c_str(); }
+const char* b200_w4a16_version(void) { return "b200-w4a16 0.1 (sm_100a)"; }
+int64_t b200_w4a16_launch_count(void) { return g_launches.load(); }
+
+int b200_w4a16_reduce_max_m(int64_t m) {
+  // mirror of marlin::determine_reduce_max_m(prob_m, max_par = 16), gptq_marlin_utils.cu:206-225
+  if (m <= 16) return 16;
+  if (m <= 32) return 32;
+  if (m <= 48) return 48;
+  if (m <= 64) return 64;
+  int64_t par = (m + 63) / 64;
+  if (par > 16) par = 16;
+  return static_cast<int>(64 * par);
+}
+
+int64_t b200_w4a16_workspace_ints(int64_t n) { return (n / 64) * 16; }
+
+int64_t b200_w4a16_reduce_bytes(int64_t m, int64_t n, int64_t k) {
+  if (m <= 0 || n <= 0 || k <= 0 || n % 64 || k % 64) return -1;
+  const int rows = static_cast<int>(m < 32 ? m : 32);
+  // worst case over the geometries the heuristic (or force_config) may use
+  int64_t worst = 0;
+  for (int geo = 0; geo < kGeoms; ++geo) {
+    const int tn = kGeom[geo].chunks * 64, kb = kGeom[geo].krows * 16;
+    if (k % kb) continue;
+    const long long ncols = (n + tn - 1) / tn, kblks = k / kb, units = ncols * kblks;
+    const int grid = static_cast<int>(units < sm_count() ? units : sm_count());
+    const int64_t bytes = ncols * decode_slot_max(static_cast<int>(kblks), units, grid) * rows * tn * 4ll;
+    if (bytes > worst) worst = bytes;
+  }
+  return worst;
+}
+
+int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int dtype) {
+  if (m <= 0 || n <= 0 || k <= 0 || (dtype != 0 && dtype != 1)) return -1;
+  const int mm = static_cast<int>(m < 32 ? m : 32);
+  return 1 + decode_index(dtype, nt_for_m(mm), group_size != -1, pick_geometry(mm, (int)n, (int)k));
+}
+
+const char* b200_w4a16_config_name(int config) {
+  const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
+  if (config < 1 || config > count) return "";
+  return g_decode[config - 1].name;
+}
+
+int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales, const int32_t* g_idx,
+                       const int32_t* perm, int32_t* workspace, void* c, int64_t m, int64_t n, int64_t k,
+                       int group_size, int dtype, int is_k_full, int has_act_order, void* a_tmp,
+                       float* c_tmp, void* stream, const b200_w4a16_opts* opts) {
+  (void)g_idx;
+  // ---- validation: the reference's checks (gptq_marlin.cu:71-72, gptq_marlin_mm.cu:53-54,84-131) ----
+  if (!(m > 0 && n > 0 && k > 0))
+    return fail(B200_W4A16_EINVAL, "Invalid MNK = [%lld, %lld, %lld]", (long long)m, (long long)n, (long long)k);
+  if (n % 64 != 0)
+    return fail(B200_W4A16_EINVAL, "size_n = %lld, is not divisible by min_thread_n = 64", (long long)n);
+  if (k % 64 != 0)
+    return fail(B200_W4A16_EINVAL, "size_k = %lld, is not divisible by min_thread_k = 64", (long long)k);
+  if (dtype != B200_W4A16_FP16 && dtype != B200_W4A16_BF16)
+    return fail(B200_W4A16_EINVAL, "dtype must be 0 (fp16) or 1 (bf16), got %d", dtype);
+  if (group_size != 128 && group_size != -1)
+    return fail(B200_W4A16_EINVAL, "Unsupported group size %d (128 or -1)", group_size);
+  if (group_size == 128 && k % 128 != 0)
+    return fail(B200_W4A16_EINVAL, "prob_k = %lld is not divisible by group_size = 128", (long long)k);
+  if (m > INT32_MAX || n > INT32_MAX || k > INT32_MAX || m * n > (1ll << 40))
+    return fail(B200_W4A16_EINVAL, "problem too large: MNK = [%lld, %lld, %lld]", (long long)m, (long long)n, (long long)k);
+  if (!a || !qweight || !c || !workspace || (group_size == 128 && !scales) || (group_size == -1 && !scales))
+    return fail(B200_W4A16_EINVAL, "null pointer argument (a/qweight/scales/workspace/c)");
+  if (has_act_order) {
+    if (!is_k_full)
+      return fail(B200_W4A16_EINVAL,
+                  "has_act_order with is_k_full = false (g_idx-indexed scales) is not supported; "
+                  "CPM.cu never takes that path (w4a16_gptq_marlin_linear.cuh:55,66) and its converter "
+                  "rejects desc_act checkpoints (gptq2marlin.py:91)");
+    if (group_size == -1)
+      return fail(B200_W4A16_EINVAL, "group_size must not be -1 when has_act_order=true and is_k_full=true");
+    if (!perm || !a_tmp) return fail(B200_W4A16_EINVAL, "has_act_order needs perm and a_tmp");
+  }
+  if (!c_tmp) return fail(B200_W4A16_EINVAL, "c_tmp (fp32 reduce scratch) is required");
+  if (opts && opts->c_tmp_bytes > 0 && opts->c_tmp_bytes < b200_w4a16_reduce_bytes(m, n, k))
+    return fail(B200_W4A16_EINVAL, "c_tmp too small: %lld bytes given, %lld needed for MNK = [%lld, %lld, %lld]",
+                (long long)opts->c_tmp_bytes, (long long)b200_w4a16_reduce_bytes(m, n, k), (long long)m,
+                (long long)n, (long long)k);
+
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const size_t esz = 2;
+  if (has_act_order) {
+    const long long total = m * k;
+    const int blocks = static_cast<int>(total / 256 + 1 < 4096 ? total / 256 + 1 : 4096);
+    if (dtype == 0)
+      gather_columns_kernel<__half><<<blocks, 256, 0, st>>>((const __half*)a, perm, (__half*)a_tmp, (int)m, (int)k);
+    else
+      gather_columns_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)a, perm, (__nv_bfloat16*)a_tmp, (int)m, (int)k);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    a = a_tmp;
+  }
+
+  const bool grouped = group_size != -1;
+  const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
+  // ---- M loop: slabs of <= 32 tokens through the streaming kernel ----
+  for (int64_t m0 = 0; m0 < m; m0 += 32) {
+    const int mm = static_cast<int>(m - m0 < 32 ? m - m0 : 32);
+    int idx;
+    if (opts && opts->force_config > 0) {
+      idx = opts->force_config - 1;
+      if (idx >= count) return fail(B200_W4A16_EINVAL, "force_config %d out of range", opts->force_config);
+      const DecodeConfig& f = g_decode[idx];
+      if (f.dtype != dtype || f.grouped != grouped || f.nt * 8 < mm || k % (f.krows * 16) != 0)
+        return fail(B200_W4A16_EINVAL, "force_config %d (%s) does not fit m=%d k=%lld dtype=%d group=%d",
+                    opts->force_config, f.name, mm, (long long)k, dtype, group_size);
+    } else {
+      idx = decode_index(dtype, nt_for_m(mm), grouped, pick_geometry(mm, (int)n, (int)k));
+    }
+    GemmCall g;
+    g.a = static_cast<const char*>(a) + static_cast<size_t>(m0) * k * esz;
+    g.qweight = qweight;
+    g.scales = scales;
+    g.workspace = workspace;
+    g.c = static_cast<char*>(c) + static_cast<size_t>(m0) * n * esz;
+    g.c_tmp = c_tmp;
+    g.bias = opts ? opts->bias : nullptr;
+    g.residual = (opts && opts->residual)
+                     ? static_cast<const char*>(opts->residual) + static_cast<size_t>(m0) * n * esz
+                     : nullptr;
+    g.m = mm;
+    g.n = static_cast<int>(n);
+    g.k = static_cast<int>(k);
+    g.group_size = group_size;
+    g.pdl = opts && opts->pdl;
+    g.stream = st;
+    if (int rc = g_decode[idx].launch(g)) return rc;
+  }
+  return B200_W4A16_OK;
+}
+
+int b200_w4a16_gemm(const void* a, const int32_t* qweight, const void* scales, const int32_t* g_idx,
+                    const int32_t* perm, int32_t* workspace, void* c, int64_t m, int64_t n, int64_t k,
+                    int group_size, int dtype, int is_k_full, int has_act_order, void* a_tmp, float* c_tmp,
+                    void* stream) {
+  return b200_w4a16_gemm_ex(a, qweight, scales, g_idx, perm, workspace, c, m, n, k, group_size, dtype,
+                            is_k_full, has_act_order, a_tmp, c_tmp, stream, nullptr);
+}
+
+int b200_w4a16_linear_forward(const void* input, const int32_t* qweight, const void* scales, const void* bias,
+                              int32_t* workspace, void* output, void* tgt, int inplace, int64_t num_tokens,
+                              int64_t dim_out, int64_t dim_in, int group_size, int dtype, void* a_tmp,
+                              float* c_tmp, void* stream) {
+  // W4A16GPTQMarlinLinear::prefill, w4a16_gptq_marlin_linear.cuh:104-146
+  b200_w4a16_opts o;
+  std::memset(&o, 0, sizeof(o));
+  o.bias = bias;
+  void* dst = output;
+  if (tgt && inplace) {
+    o.residual = tgt;
+    dst = tgt;
+  } else if (tgt) {
+    dst = tgt;
+  }
+  if (!dst) return fail(B200_W4A16_EINVAL, "linear_forward: no output buffer");
+  return b200_w4a16_gemm_ex(input, qweight, scales, nullptr, nullptr, workspace, dst, num_tokens, dim_out,
+                            dim_in, group_size, dtype, /*is_k_full=*/1, /*has_act_order=*/0, a_tmp, c_tmp,
+                            stream, &o);
+}
+
+int b200_w4a16_dequant(const int32_t* qweight, const void* scales, void* w_out, int64_t n, int64_t k,
+                       int group_size, int dtype, void* stream) {
+  if (!(n > 0 && k > 0) || n % 64 || k % 16)
+    return fail(B200_W4A16_EINVAL, "dequant: need n %% 64 == 0 and k %% 16 == 0, got n=%lld k=%lld", (long long)n, (long long)k);
+  if (group_size != 128 && group_size != -1) return fail(B200_W4A16_EINVAL, "Unsupported group size %d", group_size);
+  if (group_size == 128 && k % 128) return fail(B200_W4A16_EINVAL, "dequant: k %% 128 != 0");
+  if (dtype != 0 && dtype != 1) return fail(B200_W4A16_EINVAL, "dtype must be 0 or 1");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const long long blocks = (k / 16) * (n / 64);
+  const int grid = static_cast<int>((blocks + 7) / 8 < 148 * 8 ? (blocks + 7) / 8 : 148 * 8);
+  const uint4* q = reinterpret_cast<const uint4*>(qweight);
+  if (dtype == 0) {
+    if (group_size == -1)
+      w4a16_dequant_kernel<__half, false><<<grid, 256, 0, st>>>(q, (const __half*)scales, (__half*)w_out, (int)n, (int)k, 1);
+    else
+      w4a16_dequant_kernel<__half, true><<<grid, 256, 0, st>>>(q, (const __half*)scales, (__half*)w_out, (int)n, (int)k, group_size);
+  } else {
+    if (group_size == -1)
+      w4a16_dequant_kernel<__nv_bfloat16, false><<<grid, 256, 0, st>>>(q, (const __nv_bfloat16*)scales, (__nv_bfloat16*)w_out, (int)n, (int)k, 1);
+    else
+      w4a16_dequant_kernel<__nv_bfloat16, true><<<grid, 256, 0, st>>>(q, (const __nv_bfloat16*)scales, (__nv_bfloat16*)w_out, (int)n, (int)k, group_size);
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(B200_W4A16_ECUDA, "dequant launch: %s", cudaGetErrorString(e));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return 0;
+}
+
+int b200_w4a16_repack_gptq(const int32_t* qweight_gptq, int32_t* qweight_marlin, int64_t n, int64_t k, void* stream) {
+  if (!(n > 0 && k > 0) || n % 64 || k % 16)
+    return fail(B200_W4A16_EINVAL, "repack: need n %% 64 == 0 and k %% 16 == 0, got n=%lld k=%lld", (long long)n, (long long)k);
+  const long long words = (k / 16) * 2 * n;
+  const int grid = static_cast<int>((words + 255) / 256 < 148 * 16 ? (words + 255) / 256 : 148 * 16);
+  repack_gptq_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const uint32_t*>(qweight_gptq), reinterpret_cast<uint32_t*>(qweight_marlin), (int)n, (int)k);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(B200_W4A16_ECUDA, "repack launch: %s", cudaGetErrorString(e));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,182 @@
+"""ctypes binding of libb200_w4a16.so (C ABI: include/b200_w4a16.h).
+
+PyTorch is used for device memory and streams only; every compute call goes through the C ABI
+with raw device pointers, the way the reference's pybind module passes them
+(reference: src/entry.cu:536-570).  There is NO fallback: if the library is missing or a call
+fails, an exception is raised (ValueError / RuntimeError, matching the reference's
+VALUE_CHECK / ERROR_CHECK -> pybind mapping, src/utils.cuh:54-66).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_int32, c_int64, c_void_p, POINTER
+
+FP16, BF16 = 0, 1  # dtype codes of the reference: cpmcu/llm_w4a16_gptq_marlin.py:12-15
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_NAME = "libb200_w4a16.so"
+
+
+class B200W4A16Error(RuntimeError):
+    pass
+
+
+class Opts(ctypes.Structure):
+    _fields_ = [
+        ("bias", c_void_p),
+        ("residual", c_void_p),
+        ("c_tmp_bytes", c_int64),
+        ("force_config", c_int),
+        ("pdl", c_int),
+        ("reserved", c_int * 5),
+    ]
+
+
+def library_path() -> str:
+    return os.environ.get("B200_W4A16_LIB", os.path.join(_HERE, _LIB_NAME))
+
+
+_lib = None
+
+# name -> (restype, argtypes): every symbol include/b200_w4a16.h declares
+SYMBOLS = {
+    "b200_w4a16_gemm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                c_void_p]),
+    "b200_w4a16_gemm_ex": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                   c_void_p, POINTER(Opts)]),
+    "b200_w4a16_linear_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                          c_int, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p,
+                                          c_void_p]),
+    "b200_w4a16_dequant": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p]),
+    "b200_w4a16_repack_gptq": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
+    "b200_w4a16_reduce_max_m": (c_int, [c_int64]),
+    "b200_w4a16_reduce_bytes": (c_int64, [c_int64, c_int64, c_int64]),
+    "b200_w4a16_workspace_ints": (c_int64, [c_int64]),
+    "b200_w4a16_launch_count": (c_int64, []),
+    "b200_w4a16_pick_config": (c_int, [c_int64, c_int64, c_int64, c_int, c_int]),
+    "b200_w4a16_config_name": (c_char_p, [c_int]),
+    "b200_w4a16_last_error": (c_char_p, []),
+    "b200_w4a16_version": (c_char_p, []),
+}
+
+
+def lib() -> ctypes.CDLL:
+    """Load the CUDA library (once).  Raises if it has not been built: there is no CPU path."""
+    global _lib
+    if _lib is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise B200W4A16Error(
+                f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a). cpmcu_b200 has no CPU or PyTorch fallback.")
+        handle = ctypes.CDLL(path)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(handle, name)  # AttributeError if the library does not export it
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def _raise(code: int):
+    msg = lib().b200_w4a16_last_error().decode()
+    if code == 1:
+        raise ValueError(msg)
+    raise RuntimeError(f"b200_w4a16 error {code}: {msg}")
+
+
+def _ptr(t):
+    return None if t is None else c_void_p(t.data_ptr())
+
+
+def _stream(stream=None):
+    import torch
+    s = torch.cuda.current_stream() if stream is None else stream
+    return c_void_p(s.cuda_stream)
+
+
+def dtype_code(torch_dtype) -> int:
+    import torch
+    if torch_dtype == torch.float16:
+        return FP16
+    if torch_dtype == torch.bfloat16:
+        return BF16
+    raise ValueError(f"W4A16 supports float16 / bfloat16 activations, got {torch_dtype}")
+
+
+def reduce_max_m(m: int) -> int:
+    return lib().b200_w4a16_reduce_max_m(m)
+
+
+def reduce_bytes(m: int, n: int, k: int) -> int:
+    return lib().b200_w4a16_reduce_bytes(m, n, k)
+
+
+def workspace_ints(n: int) -> int:
+    return lib().b200_w4a16_workspace_ints(n)
+
+
+def launch_count() -> int:
+    return lib().b200_w4a16_launch_count()
+
+
+def pick_config(m, n, k, group_size=128, dtype=FP16) -> int:
+    return lib().b200_w4a16_pick_config(m, n, k, group_size, dtype)
+
+
+def config_name(cfg: int) -> str:
+    return lib().b200_w4a16_config_name(cfg).decode()
+
+
+def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm=None, a_tmp=None,
+         bias=None, residual=None, force_config=0, pdl=False, stream=None):
+    """C[M,N] = A[M,K] . dequant(qweight, scales)  (+ residual, + bias) on the current stream.
+
+    a: [M,K] fp16/bf16 cuda, qweight: int32 [K/16, 2N] cuda (Marlin), scales: [K/g, N] (Marlin-permuted),
+    workspace: int32 [(N/64)*16] zeroed, c_tmp: float32 scratch of >= reduce_bytes(M,N,K) bytes."""
+    import torch
+    assert a.is_cuda and a.is_contiguous() and qweight.is_contiguous() and scales.is_contiguous()
+    m, k = a.shape
+    n = qweight.shape[1] // 2
+    if out is None:
+        out = torch.empty((m, n), dtype=a.dtype, device=a.device)
+    o = Opts()
+    o.bias = None if bias is None else bias.data_ptr()
+    o.residual = None if residual is None else residual.data_ptr()
+    o.c_tmp_bytes = c_tmp.numel() * c_tmp.element_size()
+    o.force_config = force_config
+    o.pdl = 1 if pdl else 0
+    rc = lib().b200_w4a16_gemm_ex(_ptr(a), _ptr(qweight), _ptr(scales), None, _ptr(perm), _ptr(workspace),
+                                  _ptr(out), m, n, k, group_size, dtype_code(a.dtype), 1,
+                                  0 if perm is None else 1, _ptr(a_tmp), _ptr(c_tmp), _stream(stream),
+                                  ctypes.byref(o))
+    if rc:
+        _raise(rc)
+    return out
+
+
+def dequant(qweight, scales, k, n, *, group_size=128, dtype=None, stream=None):
+    """W[K,N] = RN(T(q-8) * T(scale)) — the dequantisation the GEMM kernels apply in registers."""
+    import torch
+    dt = scales.dtype if dtype is None else dtype
+    out = torch.empty((k, n), dtype=dt, device=qweight.device)
+    rc = lib().b200_w4a16_dequant(_ptr(qweight), _ptr(scales), _ptr(out), n, k, group_size, dtype_code(dt),
+                                  _stream(stream))
+    if rc:
+        _raise(rc)
+    return out
+
+
+def repack_gptq(qweight_gptq, stream=None):
+    """AutoGPTQ int32[K/8,N] -> Marlin int32[K/16,2N] on the device."""
+    import torch
+    k8, n = qweight_gptq.shape
+    k = k8 * 8
+    out = torch.empty((k // 16, 2 * n), dtype=torch.int32, device=qweight_gptq.device)
+    rc = lib().b200_w4a16_repack_gptq(_ptr(qweight_gptq), _ptr(out), n, k, _stream(stream))
+    if rc:
+        _raise(rc)
+    return out

@@ -1,0 +1,124 @@
+/*
+ * b200_w4a16.h — C ABI of the B200-native W4A16 GPTQ-Marlin linear (libb200_w4a16.so).
+ *
+ * This is the drop-in boundary for the quantised-linear hot path of jk3456a/CPM.cu.  Every entry
+ * point names the reference interface it replaces (file:line relative to the reference tree).
+ * Plain pointers and sizes only: device pointers are raw CUDA device addresses, exactly as the
+ * reference passes them through its pybind module (src/entry.cu:536-570), `stream` is a
+ * cudaStream_t / CUstream passed as void*.  The library allocates nothing on the device, never
+ * synchronises the host with the device, and every launch is CUDA-graph capturable
+ * (reference contract: src/entry.cu:540-562).
+ *
+ * Data formats are the reference's, bit for bit:
+ *   qweight  int32 [K/16][2N]   Marlin-packed uint4b8 (scripts/model_convert/gptq2marlin.py:109-134)
+ *   scales   T     [K/g ][N]    per-group scales, permuted per 64 columns (gptq2marlin.py:99-107);
+ *                               g = 128, or one row permuted per 32 columns when group_size == -1
+ *   a, c     T     [M][K], [M][N] row-major,  T = fp16 (dtype 0) or bf16 (dtype 1)
+ *                               (dtype codes: cpmcu/llm_w4a16_gptq_marlin.py:12-15)
+ *
+ * Error convention (reference: src/utils.cuh:54-66 -> Python ValueError / RuntimeError via pybind):
+ *   0  success
+ *   1  invalid argument  (the reference's VALUE_CHECK  -> std::invalid_argument -> ValueError)
+ *   2  runtime error     (the reference's ERROR_CHECK  -> std::runtime_error    -> RuntimeError)
+ *   3  CUDA error reported by the runtime/driver while encoding descriptors or launching
+ * b200_w4a16_last_error() returns the message of the last failure on the calling thread.
+ */
+#ifndef B200_W4A16_H_
+#define B200_W4A16_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_W4A16_OK 0
+#define B200_W4A16_EINVAL 1
+#define B200_W4A16_ERUNTIME 2
+#define B200_W4A16_ECUDA 3
+
+#define B200_W4A16_FP16 0
+#define B200_W4A16_BF16 1
+
+/* Optional fused post-ops and tuning knobs for b200_w4a16_gemm_ex.  Zero-initialise it. */
+typedef struct b200_w4a16_opts {
+  /* post-ops of W4A16GPTQMarlinLinear::prefill (src/model/w4a16_gptq_marlin/w4a16_gptq_marlin_linear.cuh:140-145),
+   * fused into the GEMM epilogue with the reference's rounding points:
+   *   out = RN_T(gemm);  if (residual) out = RN_T(residual + out);  if (bias) out = RN_T(out + bias)   */
+  const void* bias;      /* T[N] or NULL                        (batched_add, src/model/elementwise.cuh:8-14)  */
+  const void* residual;  /* T[M][N] or NULL; may alias `c`      (elementwise_add, src/model/elementwise.cuh:17-23) */
+  int64_t c_tmp_bytes;   /* size of c_tmp if known (validated), or 0 = caller guarantees b200_w4a16_reduce_bytes() */
+  int force_config;      /* 0 = heuristic; >0 = kernel configuration id (tuning / tests only)        */
+  int pdl;               /* 1 = launch with programmatic dependent launch (prologue overlaps the previous kernel) */
+  int reserved[5];
+} b200_w4a16_opts;
+
+/* Replaces gptq_marlin_gemm<T> (src/qgemm/gptq_marlin/gptq_marlin.cuh:11-27, gptq_marlin.cu:42-86)
+ * as called by W4A16GPTQMarlinLinear::prefill (w4a16_gptq_marlin_linear.cuh:115-138):
+ *     C[M][N] = A[M][K] . dequant(qweight, scales)
+ * Fixed by the call site and therefore not parameters: b_q_type = kU4B8, has_zp = false,
+ * use_fp32_reduce = true, b_zeros = NULL.
+ *   g_idx, perm   NULL unless has_act_order (then perm[K] gathers the columns of A into a_tmp,
+ *                 reference: gptq_marlin_utils.cu:28-77; only is_k_full = 1 is supported, as in CPM.cu)
+ *   workspace     int32[(N/64)*16], zero on entry, zero again when the call completes
+ *                 (reference lock contract: marlin_device_ops.cuh:347-377; w4a16_gptq_marlin_linear.cuh:76)
+ *   a_tmp         T[M][K] scratch, touched only when has_act_order
+ *   c_tmp         fp32 split-K scratch of at least b200_w4a16_reduce_bytes(m, n, k) bytes
+ * Constraints (as the reference, gptq_marlin.cu:71-72, gptq_marlin_mm.cu:53-54,103-131):
+ *   M,N,K > 0;  N % 64 == 0;  K % 64 == 0;  group_size in {128, -1};  K % 128 == 0 when group_size == 128. */
+int b200_w4a16_gemm(const void* a, const int32_t* qweight, const void* scales,
+                    const int32_t* g_idx, const int32_t* perm, int32_t* workspace, void* c,
+                    int64_t m, int64_t n, int64_t k, int group_size, int dtype,
+                    int is_k_full, int has_act_order, void* a_tmp, float* c_tmp, void* stream);
+
+/* Same, with fused post-ops / knobs (opts may be NULL). */
+int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales,
+                       const int32_t* g_idx, const int32_t* perm, int32_t* workspace, void* c,
+                       int64_t m, int64_t n, int64_t k, int group_size, int dtype,
+                       int is_k_full, int has_act_order, void* a_tmp, float* c_tmp, void* stream,
+                       const b200_w4a16_opts* opts);
+
+/* Replaces W4A16GPTQMarlinLinear<T>::prefill (w4a16_gptq_marlin_linear.cuh:104-146):
+ * GEMM into `output` (or `tgt`), then `inplace` -> tgt += out, `bias` -> tgt += bias, in one launch.
+ *   tgt == NULL            -> result in output
+ *   tgt != NULL, !inplace  -> result in tgt
+ *   tgt != NULL,  inplace  -> tgt = tgt + gemm   (output is not written: the fused epilogue needs no staging) */
+int b200_w4a16_linear_forward(const void* input, const int32_t* qweight, const void* scales,
+                              const void* bias, int32_t* workspace, void* output, void* tgt,
+                              int inplace, int64_t num_tokens, int64_t dim_out, int64_t dim_in,
+                              int group_size, int dtype, void* a_tmp, float* c_tmp, void* stream);
+
+/* W[K][N] = RN_T(T(q - 8) * T(scale)) written out in T: the bit-exact dequantisation the GEMM
+ * kernels apply in registers (reference device code: marlin_device_ops.cuh:91-137, 294-303).
+ * group_size == -1 writes T(q - 8) (the reference scales the rounded output instead). */
+int b200_w4a16_dequant(const int32_t* qweight, const void* scales, void* w_out, int64_t n, int64_t k,
+                       int group_size, int dtype, void* stream);
+
+/* AutoGPTQ int32[K/8][N] -> Marlin int32[K/16][2N] on the device
+ * (replaces marlin_repack_qweight, scripts/model_convert/gptq2marlin.py:109-134). */
+int b200_w4a16_repack_gptq(const int32_t* qweight_gptq, int32_t* qweight_marlin, int64_t n, int64_t k,
+                           void* stream);
+
+/* Sizing helpers.
+ * b200_w4a16_reduce_max_m  == marlin::determine_reduce_max_m(prob_m, 16) (gptq_marlin_utils.cu:206-225).
+ * b200_w4a16_reduce_bytes  bytes of c_tmp this library needs for (m, n, k) on the current device; it is
+ *                          <= 4 * reduce_max_m(m) * 32768 for all shapes with n <= 32768 the reference
+ *                          serves (callers size c_tmp that way: w4a16_gptq_marlin_layer.cuh:34-37).
+ * b200_w4a16_workspace_ints == (n / 64) * 16 (w4a16_gptq_marlin_linear.cuh:76). */
+int b200_w4a16_reduce_max_m(int64_t m);
+int64_t b200_w4a16_reduce_bytes(int64_t m, int64_t n, int64_t k);
+int64_t b200_w4a16_workspace_ints(int64_t n);
+
+/* Introspection: kernels launched by this library since load (for bench.py's gpu_launches),
+ * the configuration id the heuristic picks for a shape, last error, version string. */
+int64_t b200_w4a16_launch_count(void);
+int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int dtype);
+const char* b200_w4a16_config_name(int config);
+const char* b200_w4a16_last_error(void);
+const char* b200_w4a16_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_W4A16_H_ */

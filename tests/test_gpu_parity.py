@@ -1,0 +1,258 @@
+"""GPU parity (-m gpu): the CUDA path, called through the C ABI, against
+  (1) the numpy oracle (oracle/marlin_oracle.py) on seeded inputs at sizes it finishes in seconds,
+  (2) the UNMODIFIED reference Marlin kernel (oracle/_ref/libmarlin_ref.so) on the same inputs,
+  (3) size-independent properties at BASELINE.json's full sizes.
+Bar: dequant bit-exact; GEMM output max rel err <= 1e-2 (north_star), mean abs err reported."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import marlin_oracle as mo
+from tests import ref_marlin
+
+pytestmark = pytest.mark.gpu
+
+TOL_MAX_REL = 1e-2  # north_star: "max rel err <= 1e-2, and report mean abs err"
+DEV = "cuda"
+
+
+def _b():
+    import cpmcu_b200
+    return cpmcu_b200
+
+
+def t_store(x, dtype):
+    """oracle storage array -> torch tensor on the GPU"""
+    if dtype == mo.FP16:
+        return torch.from_numpy(np.ascontiguousarray(x)).to(DEV)
+    return torch.from_numpy(np.ascontiguousarray(x).view(np.int16)).to(DEV).view(torch.bfloat16)
+
+
+def t_load(t, dtype):
+    if dtype == mo.FP16:
+        return t.cpu().numpy()
+    return t.view(torch.int16).cpu().numpy().view(np.uint16)
+
+
+def scratch(m, n, k):
+    b = _b()
+    ws = torch.zeros(b.workspace_ints(n), dtype=torch.int32, device=DEV)
+    ref_floats = ref_marlin.reduce_max_m(m) * n if ref_marlin.available() else 0
+    c_tmp = torch.empty(max(b.reduce_bytes(m, n, k) // 4, ref_floats, 1), dtype=torch.float32, device=DEV)
+    return ws, c_tmp
+
+
+def run_ours(prob, m, n, k, dtype, group=128, **kw):
+    b = _b()
+    a = t_store(prob["a"], dtype)
+    qw = torch.from_numpy(prob["qweight"]).to(DEV)
+    sc = t_store(prob["scales_marlin"], dtype)
+    ws, c_tmp = scratch(m, n, k)
+    out = b.gemm(a, qw, sc, ws, c_tmp, group_size=group, **kw)
+    torch.cuda.synchronize()
+    assert int(ws.abs().max()) == 0, "workspace must be returned zeroed (reference lock contract)"
+    return out, (a, qw, sc, ws, c_tmp)
+
+
+@pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
+@pytest.mark.parametrize("group", [128, -1])
+def test_dequant_bit_exact(dtype, group):
+    """int4 unpack + group dequant must be bit-exact vs the oracle (incl. subnormal / huge scales)."""
+    b = _b()
+    k, n = 512, 256
+    prob = mo.make_problem(1, k, n, group, dtype, seed=3)
+    s = mo.to_f32(prob["scales"], dtype).copy()
+    s[0, :8] = [6e-8, 1e-7, 3e-5, 6.1e-5, 1000.0, 8000.0, -0.01, 0.0]      # subnormal .. overflow-ish .. negative
+    s_st = mo.to_storage(s, dtype)
+    sm = mo.permute_scales(s_st, k, n, group)
+    want = mo.dequant(prob["qweight"], sm, k, n, group, dtype)
+    got = b.dequant(torch.from_numpy(prob["qweight"]).to(DEV), t_store(sm, dtype), k, n, group_size=group)
+    torch.cuda.synchronize()
+    got = t_load(got, dtype)
+    assert np.array_equal(got.view(np.uint16), want.view(np.uint16))
+
+
+def test_dequant_exhaustive_scales_fp16():
+    """16 nibbles x all 63488 finite fp16 scale bit patterns (SURVEY.md section 8(c) pin 1), on the device."""
+    b = _b()
+    bits = np.arange(0x10000, dtype=np.uint32).astype(np.uint16)
+    finite = np.isfinite(bits.view(np.float16))
+    sbits = bits[finite]
+    n = (len(sbits) + 63) // 64 * 64
+    s = np.zeros(n, dtype=np.uint16)
+    s[:len(sbits)] = sbits
+    k = 128
+    wq = np.tile(np.arange(16, dtype=np.uint8).repeat(8)[:, None], (1, n))         # every nibble in every column
+    qw = mo.marlin_pack(wq)
+    s16 = s.view(np.float16).reshape(1, n)
+    sm = mo.permute_scales(s16, k, n, 128)
+    want = mo.dequant(qw, sm, k, n, 128, mo.FP16)
+    got = b.dequant(torch.from_numpy(qw).to(DEV), torch.from_numpy(sm).to(DEV), k, n).cpu().numpy()
+    assert np.array_equal(got.view(np.uint16), want.view(np.uint16))
+
+
+SMALL = [  # (m, k, n): config 1 of BASELINE.json first, then ragged / edge shapes
+    (1, 4096, 4096), (1, 128, 64), (3, 256, 192), (4, 1024, 320), (8, 512, 1088), (10, 2048, 576),
+    (12, 4096, 4608), (16, 1024, 2048), (17, 640, 448), (32, 1152, 1024), (33, 512, 512), (60, 768, 640),
+    (64, 1024, 1024), (100, 256, 256),
+]
+
+
+@pytest.mark.parametrize("m,k,n", SMALL)
+@pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
+def test_gemm_vs_oracle_and_reference(m, k, n, dtype):
+    prob = mo.make_problem(m, k, n, 128, dtype, seed=m * 7 + n)
+    out, (a, qw, sc, ws, c_tmp) = run_ours(prob, m, n, k, dtype)
+    c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, dtype)
+    st = mo.error_stats(t_load(out, dtype), exact, dtype)
+    # half an ulp of T at the output is the floor of any implementation: 2^-11 (fp16), 2^-8 (bf16)
+    assert st["max_rel"] <= TOL_MAX_REL, st
+    if ref_marlin.available():
+        ref = ref_marlin.gemm(a, qw, sc, ws, c_tmp)
+        torch.cuda.synchronize()
+        st_ref = mo.error_stats(t_load(ref, dtype), exact, dtype)
+        st_x = mo.error_stats(t_load(out, dtype), mo.to_f32(t_load(ref, dtype), dtype), dtype)
+        assert st_x["max_rel"] <= TOL_MAX_REL, ("ours vs reference Marlin", st_x)
+        # we must be at least as close to the exact result as the reference kernel is (x2 slack)
+        assert st["mean_abs"] <= 2 * st_ref["mean_abs"] + 1e-7, (st, st_ref)
+    print(f"\n[m={m} k={k} n={n} dt={dtype}] vs exact: max_rel={st['max_rel']:.3e} mean_abs={st['mean_abs']:.3e}")
+
+
+@pytest.mark.parametrize("m,k,n", [(1, 1024, 512), (16, 2048, 1024), (40, 512, 256)])
+@pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
+def test_gemm_channelwise(m, k, n, dtype):
+    """group_size = -1: scale applied to the ROUNDED output (two roundings) — marlin_kernel_impl.cuh:957-963"""
+    prob = mo.make_problem(m, k, n, -1, dtype, seed=11)
+    out, (a, qw, sc, ws, c_tmp) = run_ours(prob, m, n, k, dtype, group=-1)
+    c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, -1, dtype)
+    st = mo.error_stats(t_load(out, dtype), exact, dtype)
+    assert st["max_rel"] <= TOL_MAX_REL, st
+    if ref_marlin.available():
+        ref = ref_marlin.gemm(a, qw, sc, ws, c_tmp, group_size=-1)
+        torch.cuda.synchronize()
+        st_x = mo.error_stats(t_load(out, dtype), mo.to_f32(t_load(ref, dtype), dtype), dtype)
+        assert st_x["max_rel"] <= TOL_MAX_REL, st_x
+
+
+def test_all_decode_configs_agree():
+    """every kernel configuration (force_config) gives the same answer within tolerance, and the same
+    configuration is bit-identical run to run (the split-K reduction order is fixed)."""
+    b = _b()
+    from cpmcu_b200 import lib as L
+    m, k, n = 16, 2048, 1536
+    prob = mo.make_problem(m, k, n, 128, mo.FP16, seed=5)
+    c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, mo.FP16)
+    seen = 0
+    for cfg in range(1, 200):
+        name = L.config_name(cfg)
+        if not name:
+            break
+        if not name.startswith("__half/nt2/") or not name.endswith("true"):
+            continue
+        out1, _ = run_ours(prob, m, n, k, mo.FP16, force_config=cfg)
+        out2, _ = run_ours(prob, m, n, k, mo.FP16, force_config=cfg)
+        assert torch.equal(out1, out2), f"{name}: not deterministic"
+        st = mo.error_stats(out1.cpu().numpy(), exact, mo.FP16)
+        assert st["max_rel"] <= TOL_MAX_REL, (name, st)
+        seen += 1
+    assert seen >= 4
+
+
+def test_act_order_gather():
+    """has_act_order + is_k_full: A's columns are gathered by perm, weights are already group-sorted."""
+    b = _b()
+    m, k, n = 5, 512, 256
+    prob = mo.make_problem(m, k, n, 128, mo.FP16, seed=9)
+    perm = np.random.default_rng(2).permutation(k).astype(np.int32)
+    a = t_store(prob["a"], mo.FP16)
+    qw = torch.from_numpy(prob["qweight"]).to(DEV)
+    sc = t_store(prob["scales_marlin"], mo.FP16)
+    ws, c_tmp = scratch(m, n, k)
+    a_tmp = torch.empty_like(a)
+    out = b.gemm(a, qw, sc, ws, c_tmp, perm=torch.from_numpy(perm).to(DEV), a_tmp=a_tmp)
+    c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, mo.FP16, perm=perm)
+    st = mo.error_stats(out.cpu().numpy(), exact, mo.FP16)
+    assert st["max_rel"] <= TOL_MAX_REL, st
+    if ref_marlin.available():
+        ref = ref_marlin.gemm(a, qw, sc, ws, c_tmp, perm=torch.from_numpy(perm).to(DEV), a_tmp=torch.empty_like(a))
+        st_x = mo.error_stats(out.cpu().numpy(), ref.float().cpu().numpy(), mo.FP16)
+        assert st_x["max_rel"] <= TOL_MAX_REL, st_x
+
+
+def test_linear_operator_postops():
+    """W4A16GPTQMarlinLinear.prefill: tgt / inplace / bias semantics of w4a16_gptq_marlin_linear.cuh:104-146"""
+    b = _b()
+    m, k, n = 6, 512, 384
+    prob = mo.make_problem(m, k, n, 128, mo.FP16, seed=21)
+    rng = np.random.default_rng(4)
+    bias = rng.standard_normal(n).astype(np.float16)
+    tgt0 = rng.standard_normal((m, n)).astype(np.float16)
+    lin = b.W4A16GPTQMarlinLinear(k, n, 128, has_bias=True)
+    lin.init_weight_ptr()
+    lin.load_to_storage("x.qweight", torch.from_numpy(prob["qweight"]))
+    lin.load_to_storage("x.scales", torch.from_numpy(prob["scales_marlin"]))
+    lin.load_to_storage("x.bias", torch.from_numpy(bias))
+    with pytest.raises(ValueError):
+        lin.load_to_storage("x.qzeros", torch.zeros(1))
+    with pytest.raises(ValueError):
+        b.W4A16GPTQMarlinLinear(k, n, 64)
+    a = torch.from_numpy(prob["a"]).to(DEV)
+    _, c_tmp = scratch(m, n, k)
+    tgt = torch.from_numpy(tgt0).to(DEV)
+    lin.prefill(None, m, a, None, c_tmp, tgt=tgt, inplace=True)
+    want = mo.linear_forward(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, mo.FP16,
+                             bias=bias, tgt=tgt0, inplace=True)
+    st = mo.error_stats(tgt.cpu().numpy(), want.astype(np.float64), mo.FP16)
+    assert st["max_rel"] <= TOL_MAX_REL, st
+    out = lin.prefill(None, m, a, None, c_tmp)            # tgt None -> self.output
+    want2 = mo.linear_forward(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, mo.FP16, bias=bias)
+    st2 = mo.error_stats(out.cpu().numpy(), want2.astype(np.float64), mo.FP16)
+    assert st2["max_rel"] <= TOL_MAX_REL, st2
+    assert int(lin.workspace.abs().max()) == 0
+
+
+def test_error_convention():
+    b = _b()
+    a = torch.zeros((1, 128), dtype=torch.float16, device=DEV)
+    qw = torch.zeros((8, 2 * 96), dtype=torch.int32, device=DEV)       # N = 96: not a multiple of 64
+    sc = torch.zeros((1, 96), dtype=torch.float16, device=DEV)
+    ws = torch.zeros(64, dtype=torch.int32, device=DEV)
+    ct = torch.zeros(1 << 16, dtype=torch.float32, device=DEV)
+    with pytest.raises(ValueError, match="min_thread_n"):
+        b.gemm(a, qw, sc, ws, ct)
+    with pytest.raises(ValueError, match="group size"):
+        b.gemm(a, torch.zeros((8, 128), dtype=torch.int32, device=DEV), sc, ws, ct, group_size=32)
+
+
+FULL = [  # BASELINE.json config 2 shapes (MiniCPM4-8B) at tree-verify widths: ours vs reference Marlin
+    (1, 4096, 4608), (4, 4096, 4096), (16, 4096, 32768), (64, 16384, 4096), (12, 4096, 32768), (60, 4096, 4608),
+]
+
+
+@pytest.mark.parametrize("m,k,n", FULL)
+def test_full_size_vs_reference_and_properties(m, k, n):
+    b = _b()
+    g = torch.Generator(device=DEV).manual_seed(m + n)
+    qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=DEV, generator=g)
+    sc = (torch.rand((k // 128, n), device=DEV, generator=g) * 0.018 + 0.002).half()
+    a = torch.randn((m, k), device=DEV, generator=g).half()
+    ws, c_tmp = scratch(m, n, k)
+    out = b.gemm(a, qw, sc, ws, c_tmp)
+    # property 1: against fp64 matmul with the library's own bit-exact dequant (checked above)
+    w = b.dequant(qw, sc, k, n)
+    exact = (a.double() @ w.double()).cpu().numpy()
+    st = mo.error_stats(out.cpu().numpy(), exact, mo.FP16)
+    assert st["max_rel"] <= TOL_MAX_REL, st
+    # property 2: linearity in A (exact for power-of-two scaling)
+    out2 = b.gemm((a * 2).half(), qw, sc, ws, c_tmp)
+    assert torch.equal(out2, (out * 2).half())
+    # property 3: zero activations -> zero output; workspace still clean
+    outz = b.gemm(torch.zeros_like(a), qw, sc, ws, c_tmp)
+    assert float(outz.abs().max()) == 0.0 and int(ws.abs().max()) == 0
+    if ref_marlin.available():
+        ref = ref_marlin.gemm(a, qw, sc, ws, c_tmp)
+        st_x = mo.error_stats(out.cpu().numpy(), ref.float().cpu().numpy(), mo.FP16)
+        st_r = mo.error_stats(ref.cpu().numpy(), exact, mo.FP16)
+        assert st_x["max_rel"] <= TOL_MAX_REL, st_x
+        print(f"\n[{m}x{k}x{n}] ours vs exact {st['max_rel']:.2e}/{st['mean_abs']:.2e}  "
+              f"ref vs exact {st_r['max_rel']:.2e}/{st_r['mean_abs']:.2e}  ours vs ref {st_x['max_rel']:.2e}")

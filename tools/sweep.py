@@ -1,0 +1,112 @@
+"""Tuning sweep (run on the B200 box): every decode configuration x MiniCPM4-8B layer shape x M,
+weights rotated over > 2x L2 so every launch streams from HBM; CUDA-graph replays timed with events.
+Also times the reference Marlin (oracle/_ref) the same way.  Prints one line per measurement and
+writes gpurun_out/sweep.json."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import cpmcu_b200 as B  # noqa: E402
+from cpmcu_b200 import lib as L  # noqa: E402
+from tests import ref_marlin  # noqa: E402
+
+SHAPES = {"qkv": (4096, 4608), "o": (4096, 4096), "gate_up": (4096, 32768), "down": (16384, 4096)}
+HBM = 6541.8
+
+
+def alg_bytes(k, n):
+    return k * n // 2 + (k // 128) * n * 2
+
+
+def time_graph(fn_launch_all, reps=5):
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        fn_launch_all()  # warm-up (module load, attribute set, descriptor cache)
+        s.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            fn_launch_all()
+        g.replay()
+        s.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        best = 1e9
+        for _ in range(reps):
+            e0.record(s)
+            g.replay()
+            e1.record(s)
+            s.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+    return best
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--ms", default="1,4,16")
+    ap.add_argument("--shapes", default="qkv,o,gate_up,down")
+    ap.add_argument("--geoms", default="all")
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))
+    args = ap.parse_args()
+    dev = "cuda"
+    results = []
+    for name in args.shapes.split(","):
+        k, n = SHAPES[name]
+        nbytes = alg_bytes(k, n)
+        copies = max(4, int(300e6 // nbytes) + 1)
+        qw = torch.randint(-2**31, 2**31 - 1, (copies, k // 16, 2 * n), dtype=torch.int32, device=dev)
+        sc = (torch.rand((copies, k // 128, n), device=dev) * 0.018 + 0.002).half()
+        for m in [int(x) for x in args.ms.split(",")]:
+            a = torch.randn((m, k), device=dev).half()
+            out = torch.empty((m, n), dtype=torch.float16, device=dev)
+            ws = torch.zeros(B.workspace_ints(n), dtype=torch.int32, device=dev)
+            ct = torch.empty(max(B.reduce_bytes(m, n, k) // 4, 64 * n), dtype=torch.float32, device=dev)
+            # reference Marlin
+            ref_out = None
+            if ref_marlin.available():
+                def run_ref():
+                    for i in range(copies):
+                        ref_marlin.gemm(a, qw[i], sc[i], ws, ct, out=out)
+                t = time_graph(run_ref) / copies * 1e3
+                ref_out = ref_marlin.gemm(a, qw[0], sc[0], ws, ct).clone()
+                r = dict(shape=name, m=m, impl="reference_marlin", us=t, gbs=nbytes / t / 1e3, frac=nbytes / t / 1e3 / HBM)
+                results.append(r)
+                print(json.dumps(r), flush=True)
+            default_cfg = L.pick_config(m, n, k)
+            for cfg in range(1, 400):
+                cname = L.config_name(cfg)
+                if not cname:
+                    break
+                nt = 1 if m <= 8 else (2 if m <= 16 else 4)
+                if not cname.startswith(f"__half/nt{nt}/") or not cname.endswith("true"):
+                    continue
+                for pdl in (False, True):
+                    def run():
+                        for i in range(copies):
+                            B.gemm(a, qw[i], sc[i], ws, ct, out=out, force_config=cfg, pdl=pdl)
+                    try:
+                        t = time_graph(run) / copies * 1e3
+                    except Exception as e:  # noqa: BLE001
+                        print(f"# {name} m={m} {cname} pdl={pdl}: {e}", flush=True)
+                        continue
+                    err = None
+                    if ref_out is not None:
+                        mine = B.gemm(a, qw[0], sc[0], ws, ct, force_config=cfg)
+                        err = float(((mine.float() - ref_out.float()).abs().max() /
+                                     ref_out.float().abs().mean()).item())
+                    r = dict(shape=name, m=m, impl=cname, cfg=cfg, pdl=pdl, default=(cfg == default_cfg), us=t,
+                             gbs=nbytes / t / 1e3, frac=nbytes / t / 1e3 / HBM, err_vs_ref=err)
+                    results.append(r)
+                    print(json.dumps(r), flush=True)
+        del qw, sc
+        torch.cuda.empty_cache()
+    os.makedirs(os.path.dirname(args.out), exist_ok=True)
+    with open(args.out, "w") as f:
+        json.dump(results, f, indent=1)
+
+
+if __name__ == "__main__":
+    main()
