@@ -4,12 +4,12 @@ src/qgemm/gptq_marlin) rebuilt as hand-written sm_100a CUDA behind a C ABI (incl
 
 The package holds only what that path needs:
   csrc/            CUDA kernels + the C ABI            -> libb200_w4a16.so (built in-tree)
-  lib.py           ctypes binding of the C ABI (fails loudly when the library is missing)
+  capi.py          ctypes binding of the C ABI (fails loudly when the library is missing)
   linear.py        W4A16GPTQMarlinLinear: host-side mirror of the reference operator
   marlin_format.py the on-disk format: AutoGPTQ -> Marlin conversion (gptq2marlin.py semantics)
   sharding.py      column / row parallel slicing of Marlin tensors + the NCCL allreduce step
 """
-from .lib import (  # noqa: F401
+from .capi import (  # noqa: F401
     B200W4A16Error,
     FP16,
     BF16,

@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import ctypes
 
-from . import lib as _l
+from . import capi as _l
 
 
 class W4A16GPTQMarlinLinear:

@@ -119,8 +119,13 @@ def permute_scales(s: np.ndarray, size_k: int, size_n: int, group_size: int) -> 
     return np.ascontiguousarray(s.reshape(-1, p.size)[:, p].reshape(-1, size_n))
 
 
-def unpermute_scales(s: np.ndarray, size_k: int, size_n: int, group_size: int) -> np.ndarray:
-    p = SCALE_PERM if (group_size < size_k and group_size != -1) else SCALE_PERM_SINGLE
+def unpermute_scales(s: np.ndarray, size_k: int, size_n: int, group_size: int,
+                     kernel_view: bool = False) -> np.ndarray:
+    """inverse of permute_scales.  kernel_view=True selects the layout the reference KERNEL reads
+    (grouped whenever group_size != -1, marlin_kernel_impl.cuh:258-264), which differs from the
+    converter's choice only in the degenerate case group_size == size_k."""
+    grouped = (group_size != -1) if kernel_view else (group_size < size_k and group_size != -1)
+    p = SCALE_PERM if grouped else SCALE_PERM_SINGLE
     inv = np.empty_like(p)
     inv[p] = np.arange(p.size)
     return np.ascontiguousarray(s.reshape(-1, p.size)[:, inv].reshape(-1, size_n))
@@ -187,7 +192,7 @@ def dequant(qweight: np.ndarray, scales_marlin: np.ndarray, size_k: int, size_n:
     wq = marlin_unpack(qweight).astype(np.float32) - 8.0           # exact small integers
     if group_size == -1:
         return to_storage(wq, dtype)
-    s = unpermute_scales(np.asarray(scales_marlin), size_k, size_n, group_size)
+    s = unpermute_scales(np.asarray(scales_marlin), size_k, size_n, group_size, kernel_view=True)
     s32 = to_f32(s, dtype)                                          # [K/g][N]
     s_full = np.repeat(s32, group_size, axis=0)                     # [K][N]
     # product of two <=11-bit significands is exact in fp32 -> one RN to T, as HMUL2 does

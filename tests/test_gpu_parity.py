@@ -81,10 +81,10 @@ def test_dequant_exhaustive_scales_fp16():
     n = (len(sbits) + 63) // 64 * 64
     s = np.zeros(n, dtype=np.uint16)
     s[:len(sbits)] = sbits
-    k = 128
-    wq = np.tile(np.arange(16, dtype=np.uint8).repeat(8)[:, None], (1, n))         # every nibble in every column
+    k = 256                                                                        # two groups, same scales
+    wq = np.tile(np.arange(16, dtype=np.uint8).repeat(16)[:, None], (1, n))        # every nibble in every column
     qw = mo.marlin_pack(wq)
-    s16 = s.view(np.float16).reshape(1, n)
+    s16 = np.tile(s.view(np.float16).reshape(1, n), (2, 1))
     sm = mo.permute_scales(s16, k, n, 128)
     want = mo.dequant(qw, sm, k, n, 128, mo.FP16)
     got = b.dequant(torch.from_numpy(qw).to(DEV), torch.from_numpy(sm).to(DEV), k, n).cpu().numpy()
@@ -138,7 +138,7 @@ def test_all_decode_configs_agree():
     """every kernel configuration (force_config) gives the same answer within tolerance, and the same
     configuration is bit-identical run to run (the split-K reduction order is fixed)."""
     b = _b()
-    from cpmcu_b200 import lib as L
+    from cpmcu_b200 import capi as L
     m, k, n = 16, 2048, 1536
     prob = mo.make_problem(m, k, n, 128, mo.FP16, seed=5)
     c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, mo.FP16)
@@ -244,8 +244,13 @@ def test_full_size_vs_reference_and_properties(m, k, n):
     st = mo.error_stats(out.cpu().numpy(), exact, mo.FP16)
     assert st["max_rel"] <= TOL_MAX_REL, st
     # property 2: linearity in A (exact for power-of-two scaling)
+    # (outputs in fp16's subnormal range are excluded: there RN(2x) != 2 RN(x) legitimately)
     out2 = b.gemm((a * 2).half(), qw, sc, ws, c_tmp)
-    assert torch.equal(out2, (out * 2).half())
+    normal = out.abs() > 2.0 ** -13
+    bad = (out2 != (out * 2).half()) & normal
+    assert int(bad.sum()) == 0, (int(bad.sum()), float((out2.float() - 2 * out.float()).abs().max()))
+    # property 2b: bit-identical run to run (fixed split-K reduction order)
+    assert torch.equal(out, b.gemm(a, qw, sc, ws, c_tmp))
     # property 3: zero activations -> zero output; workspace still clean
     outz = b.gemm(torch.zeros_like(a), qw, sc, ws, c_tmp)
     assert float(outz.abs().max()) == 0.0 and int(ws.abs().max()) == 0

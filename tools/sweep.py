@@ -12,7 +12,7 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import cpmcu_b200 as B  # noqa: E402
-from cpmcu_b200 import lib as L  # noqa: E402
+from cpmcu_b200 import capi as L  # noqa: E402
 from tests import ref_marlin  # noqa: E402
 
 SHAPES = {"qkv": (4096, 4608), "o": (4096, 4096), "gate_up": (4096, 32768), "down": (16384, 4096)}
