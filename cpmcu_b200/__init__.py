@@ -6,8 +6,6 @@ The package holds only what that path needs:
   csrc/            CUDA kernels + the C ABI            -> libb200_w4a16.so (built in-tree)
   capi.py          ctypes binding of the C ABI (fails loudly when the library is missing)
   linear.py        W4A16GPTQMarlinLinear: host-side mirror of the reference operator
-  marlin_format.py the on-disk format: AutoGPTQ -> Marlin conversion (gptq2marlin.py semantics)
-  sharding.py      column / row parallel slicing of Marlin tensors + the NCCL allreduce step
 """
 from .capi import (  # noqa: F401
     B200W4A16Error,
@@ -21,5 +19,6 @@ from .capi import (  # noqa: F401
     reduce_max_m,
     workspace_ints,
     launch_count,
+    set_pdl,
 )
 from .linear import W4A16GPTQMarlinLinear  # noqa: F401

@@ -56,6 +56,7 @@ SYMBOLS = {
     "b200_w4a16_reduce_bytes": (c_int64, [c_int64, c_int64, c_int64]),
     "b200_w4a16_workspace_ints": (c_int64, [c_int64]),
     "b200_w4a16_launch_count": (c_int64, []),
+    "b200_w4a16_set_pdl": (c_int, [c_int]),
     "b200_w4a16_pick_config": (c_int, [c_int64, c_int64, c_int64, c_int, c_int]),
     "b200_w4a16_config_name": (c_char_p, [c_int]),
     "b200_w4a16_last_error": (c_char_p, []),
@@ -121,6 +122,11 @@ def workspace_ints(n: int) -> int:
 
 def launch_count() -> int:
     return lib().b200_w4a16_launch_count()
+
+
+def set_pdl(enable: bool) -> bool:
+    """process-wide default for programmatic dependent launch; returns the previous setting"""
+    return bool(lib().b200_w4a16_set_pdl(1 if enable else 0))
 
 
 def pick_config(m, n, k, group_size=128, dtype=FP16) -> int:

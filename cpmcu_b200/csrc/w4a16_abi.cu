@@ -10,6 +10,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -23,6 +24,10 @@ namespace b200 {
 
 thread_local std::string g_last_error;
 std::atomic<long long> g_launches{0};
+std::atomic<int> g_default_pdl{[] {
+  const char* e = std::getenv("B200_W4A16_PDL");
+  return (e && e[0] == '1') ? 1 : 0;
+}()};
 
 int fail(int code, const char* fmt, ...) {
   char buf[1024];
@@ -286,6 +291,7 @@ extern "C" {
 const char* b200_w4a16_last_error(void) { return g_last_error.c_str(); }
 const char* b200_w4a16_version(void) { return "b200-w4a16 0.1 (sm_100a)"; }
 int64_t b200_w4a16_launch_count(void) { return g_launches.load(); }
+int b200_w4a16_set_pdl(int enable) { return g_default_pdl.exchange(enable ? 1 : 0); }
 
 int b200_w4a16_reduce_max_m(int64_t m) {
   // mirror of marlin::determine_reduce_max_m(prob_m, max_par = 16), gptq_marlin_utils.cu:206-225
@@ -410,7 +416,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     g.n = static_cast<int>(n);
     g.k = static_cast<int>(k);
     g.group_size = group_size;
-    g.pdl = opts && opts->pdl;
+    g.pdl = opts ? (opts->pdl != 0) : (g_default_pdl.load(std::memory_order_relaxed) != 0);
     g.stream = st;
     if (int rc = g_decode[idx].launch(g)) return rc;
   }
@@ -433,6 +439,7 @@ int b200_w4a16_linear_forward(const void* input, const int32_t* qweight, const v
   b200_w4a16_opts o;
   std::memset(&o, 0, sizeof(o));
   o.bias = bias;
+  o.pdl = g_default_pdl.load(std::memory_order_relaxed);
   void* dst = output;
   if (tgt && inplace) {
     o.residual = tgt;

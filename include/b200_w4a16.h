@@ -100,11 +100,23 @@ int b200_w4a16_dequant(const int32_t* qweight, const void* scales, void* w_out, 
 int b200_w4a16_repack_gptq(const int32_t* qweight_gptq, int32_t* qweight_marlin, int64_t n, int64_t k,
                            void* stream);
 
+/* Process-wide default for programmatic dependent launch on entry points that take no opts
+ * (b200_w4a16_gemm, b200_w4a16_linear_forward): 1 = every GEMM launch carries the PDL attribute so
+ * its weight prefetch overlaps the tail of the previous kernel in the stream (safe with any
+ * predecessor: the kernels touch activations / outputs only after griddepcontrol.wait).
+ * Returns the previous setting.  Initial value: environment variable B200_W4A16_PDL (default 0). */
+int b200_w4a16_set_pdl(int enable);
+
 /* Sizing helpers.
  * b200_w4a16_reduce_max_m  == marlin::determine_reduce_max_m(prob_m, 16) (gptq_marlin_utils.cu:206-225).
- * b200_w4a16_reduce_bytes  bytes of c_tmp this library needs for (m, n, k) on the current device; it is
- *                          <= 4 * reduce_max_m(m) * 32768 for all shapes with n <= 32768 the reference
- *                          serves (callers size c_tmp that way: w4a16_gptq_marlin_layer.cuh:34-37).
+ * b200_w4a16_reduce_bytes  bytes of c_tmp this library needs for (m, n, k) on the current device.  The
+ *                          reference's callers size c_tmp ONCE for their maximum token count
+ *                          (chunk_length, >= 1024 by default): reduce_max_m(chunk) * 2*intermediate floats
+ *                          per layer (w4a16_gptq_marlin_layer.cuh:34-37; 128 MiB for MiniCPM4-8B) and
+ *                          reduce_max_m(chunk) * 2*hidden floats for EAGLE (minicpm4_eagle.cuh:134-137;
+ *                          32 MiB).  This library needs at most 16 MiB for any m <= 64 on those shapes,
+ *                          so those buffers are always large enough; a caller that sizes c_tmp per call
+ *                          must use this function instead of reduce_max_m(m) * n.
  * b200_w4a16_workspace_ints == (n / 64) * 16 (w4a16_gptq_marlin_linear.cuh:76). */
 int b200_w4a16_reduce_max_m(int64_t m);
 int64_t b200_w4a16_reduce_bytes(int64_t m, int64_t n, int64_t k);

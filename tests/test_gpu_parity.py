@@ -8,7 +8,7 @@ import pytest
 import torch
 
 from oracle import marlin_oracle as mo
-from tests import ref_marlin
+from oracle import ref_marlin
 
 pytestmark = pytest.mark.gpu
 

@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import cpmcu_b200 as B  # noqa: E402
 from cpmcu_b200 import capi as L  # noqa: E402
-from tests import ref_marlin  # noqa: E402
+from oracle import ref_marlin  # noqa: E402
 
 SHAPES = {"qkv": (4096, 4608), "o": (4096, 4096), "gate_up": (4096, 32768), "down": (16384, 4096)}
 HBM = 6541.8
