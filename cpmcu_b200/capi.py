@@ -142,7 +142,8 @@ def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm
     """C[M,N] = A[M,K] . dequant(qweight, scales)  (+ residual, + bias) on the current stream.
 
     a: [M,K] fp16/bf16 cuda, qweight: int32 [K/16, 2N] cuda (Marlin), scales: [K/g, N] (Marlin-permuted),
-    workspace: int32 [(N/64)*16] zeroed, c_tmp: float32 scratch of >= reduce_bytes(M,N,K) bytes."""
+    workspace: int32 [(N/64)*16] zeroed, c_tmp: float32 scratch of >= reduce_bytes(M,N,K) bytes
+    (may be None when reduce_bytes is 0, i.e. on the tcgen05 path, M > 64)."""
     import torch
     assert a.is_cuda and a.is_contiguous() and qweight.is_contiguous() and scales.is_contiguous()
     m, k = a.shape
@@ -152,7 +153,7 @@ def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm
     o = Opts()
     o.bias = None if bias is None else bias.data_ptr()
     o.residual = None if residual is None else residual.data_ptr()
-    o.c_tmp_bytes = c_tmp.numel() * c_tmp.element_size()
+    o.c_tmp_bytes = 0 if c_tmp is None else c_tmp.numel() * c_tmp.element_size()
     o.force_config = force_config
     o.pdl = 1 if pdl else 0
     rc = lib().b200_w4a16_gemm_ex(_ptr(a), _ptr(qweight), _ptr(scales), None, _ptr(perm), _ptr(workspace),

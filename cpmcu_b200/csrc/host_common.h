@@ -1,7 +1,44 @@
 // Host-side arithmetic shared by the dispatcher and the sizing helpers.
 #pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
 
 namespace b200 {
+
+// one GEMM launch request, shared by the dispatcher (w4a16_abi.cu) and the kernel launchers
+struct GemmCall {
+  const void* a;
+  const int32_t* qweight;
+  const void* scales;
+  int32_t* workspace;
+  void* c;
+  float* c_tmp;
+  const void* bias;
+  const void* residual;
+  int m, n, k;
+  int group_size;
+  int dtype;
+  bool pdl;
+  cudaStream_t stream;
+};
+
+// defined in w4a16_abi.cu
+int fail(int code, const char* fmt, ...);
+int sm_count();
+extern std::atomic<long long> g_launches;
+// rank 2 or 3 tiled TMA descriptor (cached); dims/strides innermost first (strides[] in bytes for dims 1..)
+int get_tensor_map(CUtensorMap* out, const void* ptr, CUtensorMapDataType type, int rank,
+                   const uint64_t* dims, const uint64_t* strides, const uint32_t* box,
+                   CUtensorMapSwizzle swz);
+
+// defined in w4a16_prefill.cu: the tcgen05 regime
+constexpr int kPrefillTiles = 4;  // (NSUB,BM) = (2,256) (1,256) (2,128) (1,128)
+int prefill_pick_tile(int m, int n, int k);
+const char* prefill_tile_name(int tile);
+int launch_prefill(const GemmCall& g, int tile);
 
 // Upper bound on the number of CTAs whose unit ranges intersect one column of `kblks` units when
 // `units` units are split evenly over `grid` CTAs (every CTA gets floor or ceil of units/grid):

@@ -1,0 +1,292 @@
+// Tensor-bound regime (chunked prefill, and every M above the streaming kernel's range): a persistent,
+// warp-specialised tcgen05 kernel.  Operand roles are SWAPPED relative to the reference's Marlin
+// kernel: the dequantised WEIGHT tile is the 128-row UMMA "A" operand (M side = output columns n)
+// and the TOKENS are the UMMA "B" operand (N side, up to 256 per instruction), so one dequantised
+// tile feeds 128 x BM x 64 MACs and the accumulator D^T[n][token] lives in tensor memory.
+//
+//   warp 4      TMA producer: raw Marlin int4 boxes + group scales (ring Q), activation boxes
+//               [BM tokens x 64 k], 128B-swizzled, rows past M zero-filled (ring A)
+//   warps 6..   dequantisers: LDS.128 of a lane's 16 B -> lop3/HSUB2/HFMA2 (exact) -> HMUL2 by the
+//               group scale (the reference's single rounding point, marlin_device_ops.cuh:294-303)
+//               -> stmatrix.x4 straight into the canonical K-major SWIZZLE_128B UMMA layout: the
+//               Marlin fragment order IS the stmatrix 8x8 fragment order, so a 32-bit word of the
+//               stream becomes four 16-byte core-matrix rows with no shuffles (ring W)
+//   warp 5      one elected lane issues tcgen05.mma (kind::f16, fp32 accumulate in TMEM);
+//               tcgen05.commit releases the A/W slots and publishes the accumulator
+//   warps 0..3  epilogue: tcgen05.ld (lane = output column n), RN to T, the operator's post-ops
+//               with the reference's rounding points, stores to C[token][n]
+// Tiles (nt, mt) are walked persistently, mt fastest, one CTA per SM; the accumulator is double
+// buffered in TMEM when it fits (<= 256 columns) so the epilogue overlaps the next tile.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+struct PrefillArgs {
+  void* c;               // T[M][N]
+  const void* scales;    // raw pointer (channelwise epilogue)
+  const void* bias;      // T[N] or null
+  const void* residual;  // T[M][N] or null (may alias c)
+  int m, n, k;
+  int n_tiles, m_tiles, kblks;
+};
+
+template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED>
+struct PrefillCfg {
+  static constexpr int BN = NSUB * 128;            // output columns per CTA tile
+  static constexpr int CHUNKS = NSUB * 2;          // 64-column Marlin chunks per tile
+  static constexpr int BK = 64;                    // k per stage = one 128-byte swizzled row
+  static constexpr int A_STAGE = BM * 128;         // activations  [BM][64] T
+  static constexpr int W_STAGE = BN * 128;         // dequantised  [BN][64] T
+  static constexpr int Q_STAGE = 4 * CHUNKS * 512; // raw int4: 4 k16-rows x CHUNKS blocks of 512 B
+  static constexpr int S_STAGE = GROUPED ? BN * 2 : 0;
+  static constexpr int ACC_COLS = NSUB * BM;       // fp32 TMEM columns per accumulator
+  static constexpr int ACC_STAGES = (512 / ACC_COLS) >= 2 ? 2 : 1;
+  static constexpr int TMEM_COLS = ACC_COLS * ACC_STAGES;  // 256 or 512: a power of two
+  static constexpr int WPC = DW / CHUNKS;          // dequant warps sharing a chunk
+  static constexpr int RPW = 4 / WPC;              // k16-rows per dequant warp per stage
+  static constexpr int OFF_A = 0;
+  static constexpr int OFF_W = OFF_A + STAGES * A_STAGE;
+  static constexpr int OFF_Q = OFF_W + STAGES * W_STAGE;
+  static constexpr int OFF_S = OFF_Q + QSTAGES * Q_STAGE;
+  static constexpr int OFF_BAR = (OFF_S + QSTAGES * S_STAGE + 127) / 128 * 128;
+  static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4;
+  static constexpr int SMEM_BYTES = OFF_BAR + NBARS * 8 + 16 + 1024;  // +1024: manual alignment
+  static constexpr int THREADS = (6 + DW) * 32;
+  static_assert(DW % CHUNKS == 0 && WPC >= 1 && 4 % WPC == 0, "dequant warp layout");
+  static_assert(TMEM_COLS == 256 || TMEM_COLS == 512, "tensor memory allocation");
+  static_assert(BM % 16 == 0 && BM <= 256, "UMMA N");
+  static_assert(SMEM_BYTES <= 232448, "shared memory budget (227 KB)");
+};
+
+template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED>
+__global__ void __launch_bounds__((6 + DW) * 32, 1)
+w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_s,
+                     const __grid_constant__ CUtensorMap tm_a, const PrefillArgs p) {
+  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED>;
+  constexpr int CHUNKS = Cfg::CHUNKS;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const uint32_t sbase = smem_u32(smem);
+  const uint32_t bar0 = sbase + Cfg::OFF_BAR;
+  const uint32_t bar_a_full = bar0;
+  const uint32_t bar_w_full = bar_a_full + STAGES * 8;
+  const uint32_t bar_consumed = bar_w_full + STAGES * 8;
+  const uint32_t bar_q_full = bar_consumed + STAGES * 8;
+  const uint32_t bar_q_empty = bar_q_full + QSTAGES * 8;
+  const uint32_t bar_acc_full = bar_q_empty + QSTAGES * 8;
+  const uint32_t bar_acc_empty = bar_acc_full + 2 * 8;
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + Cfg::OFF_BAR + Cfg::NBARS * 8);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(bar_a_full + 8 * s, 1);
+      mbar_init(bar_w_full + 8 * s, DW);
+      mbar_init(bar_consumed + 8 * s, 1);
+    }
+#pragma unroll
+    for (int s = 0; s < QSTAGES; ++s) {
+      mbar_init(bar_q_full + 8 * s, 1);
+      mbar_init(bar_q_empty + 8 * s, DW);
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(bar_acc_full + 8 * a, 1);
+      mbar_init(bar_acc_empty + 8 * a, 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 5) tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), Cfg::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  pdl_launch_dependents();
+  pdl_wait_prior_grids();
+
+  const int total_tiles = p.n_tiles * p.m_tiles;
+
+  if (warp == 4) {
+    // ===================================== TMA producer =====================================
+    if (lane == 0) {
+      tma_prefetch_desc(&tm_w);
+      tma_prefetch_desc(&tm_a);
+      if (GROUPED) tma_prefetch_desc(&tm_s);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int mt = tile % p.m_tiles, nt = tile / p.m_tiles;
+        for (int kb = 0; kb < p.kblks; ++kb, ++it) {
+          const int sq = it % QSTAGES;
+          mbar_wait(bar_q_empty + 8 * sq, ((it / QSTAGES) & 1) ^ 1);
+          mbar_arrive_expect_tx(bar_q_full + 8 * sq, Cfg::Q_STAGE + Cfg::S_STAGE);
+          tma_load_3d(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE, &tm_w, bar_q_full + 8 * sq, 0, nt * CHUNKS,
+                      kb * 4, kEvictNormal);
+          if (GROUPED)
+            tma_load_3d(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE, &tm_s, bar_q_full + 8 * sq, 0,
+                        nt * CHUNKS, kb >> 1, kEvictLast);
+          const int s = it % STAGES;
+          mbar_wait(bar_consumed + 8 * s, ((it / STAGES) & 1) ^ 1);
+          mbar_arrive_expect_tx(bar_a_full + 8 * s, Cfg::A_STAGE);
+          tma_load_2d(sbase + Cfg::OFF_A + s * Cfg::A_STAGE, &tm_a, bar_a_full + 8 * s, kb * 64, mt * BM,
+                      kEvictLast);
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ======================================= MMA issuer =======================================
+    int it = 0, acc_it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++acc_it) {
+      const int mt = tile % p.m_tiles;
+      const int acc = acc_it % Cfg::ACC_STAGES;
+      mbar_wait(bar_acc_empty + 8 * acc, ((acc_it / Cfg::ACC_STAGES) & 1) ^ 1);
+      tc_fence_after();
+      int vt = p.m - mt * BM;
+      vt = vt > BM ? BM : vt;
+      const uint32_t idesc = umma_idesc_f16<T>(128, static_cast<uint32_t>((vt + 15) & ~15));
+      const uint32_t d0 = tmem_base + acc * Cfg::ACC_COLS;
+      for (int kb = 0; kb < p.kblks; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        mbar_wait(bar_a_full + 8 * s, ph);
+        mbar_wait(bar_w_full + 8 * s, ph);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_addr = sbase + Cfg::OFF_A + s * Cfg::A_STAGE;
+          const uint32_t w_addr = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
+#pragma unroll
+          for (int sub = 0; sub < NSUB; ++sub) {
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              const uint64_t adesc = umma_desc_k_sw128(w_addr + sub * 16384 + kk * 32);
+              const uint64_t bdesc = umma_desc_k_sw128(a_addr + kk * 32);
+              tc_mma_f16(d0 + sub * BM, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+            }
+          }
+          tc_commit(bar_consumed + 8 * s);
+          if (kb == p.kblks - 1) tc_commit(bar_acc_full + 8 * acc);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 6) {
+    // ====================================== dequantisers ======================================
+    const int d = warp - 6;
+    const int ch = d % CHUNKS;      // 64-column chunk of the tile
+    const int rp = d / CHUNKS;      // k16-row phase
+    const int g = lane >> 2;
+    // stmatrix row address of this lane for word j of k16-row r:
+    //   matrix (lane>>3): rows +8 for odd matrices, k half (lane>>4); row low bits = lane & 7
+    const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8;
+    const int lkh = lane >> 4;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int kb = 0; kb < p.kblks; ++kb, ++it) {
+        const int sq = it % QSTAGES;
+        mbar_wait(bar_q_full + 8 * sq, (it / QSTAGES) & 1);
+        uint32_t s_lo[4] = {0, 0, 0, 0}, s_hi[4] = {0, 0, 0, 0};
+        if (GROUPED) {
+          const uint4 sv = *reinterpret_cast<const uint4*>(smem + Cfg::OFF_S + sq * Cfg::S_STAGE +
+                                                           ch * 128 + g * 16);
+          broadcast_scale_pair(sv.x, s_lo[0], s_hi[0]);
+          broadcast_scale_pair(sv.y, s_lo[1], s_hi[1]);
+          broadcast_scale_pair(sv.z, s_lo[2], s_hi[2]);
+          broadcast_scale_pair(sv.w, s_lo[3], s_hi[3]);
+        }
+        uint4 q[Cfg::RPW];
+#pragma unroll
+        for (int i = 0; i < Cfg::RPW; ++i) {
+          const int r = rp + Cfg::WPC * i;
+          q[i] = *reinterpret_cast<const uint4*>(smem + Cfg::OFF_Q + sq * Cfg::Q_STAGE +
+                                                 (r * CHUNKS + ch) * 512 + lane * 16);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);  // raw slot is in registers now
+
+        const int s = it % STAGES;
+        mbar_wait(bar_consumed + 8 * s, ((it / STAGES) & 1) ^ 1);  // W slot drained by the tensor core
+        const uint32_t w_addr = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
+#pragma unroll
+        for (int i = 0; i < Cfg::RPW; ++i) {
+          const int r = rp + Cfg::WPC * i;
+          const uint32_t qq[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t w[4];
+            Dequant<T>::template word<GROUPED>(qq[j], s_lo[j], s_hi[j], w);
+            // w[0]: n=g, k 0..7 | w[1]: n=g+8, k 0..7 | w[2]: n=g, k 8..15 | w[3]: n=g+8, k 8..15
+            const int nrow = ch * 64 + j * 16 + lrow;     // row of the CTA tile this lane addresses
+            const int c16 = 2 * r + lkh;                  // 16-byte k chunk inside the 128-byte row
+            const uint32_t addr = w_addr + (nrow >> 7) * 16384 + (nrow & 127) * 128 +
+                                  ((c16 ^ (nrow & 7)) << 4);
+            stmatrix_x4(addr, w[0], w[1], w[2], w[3]);
+          }
+        }
+        fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_w_full + 8 * s);
+      }
+    }
+  } else {
+    // ======================================== epilogue ========================================
+    const int qd = warp;  // TMEM lane quarter: this warp may touch lanes 32*qd .. 32*qd+31
+    int acc_it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++acc_it) {
+      const int mt = tile % p.m_tiles, nt = tile / p.m_tiles;
+      const int acc = acc_it % Cfg::ACC_STAGES;
+      mbar_wait(bar_acc_full + 8 * acc, (acc_it / Cfg::ACC_STAGES) & 1);
+      tc_fence_after();
+      const int m0 = mt * BM;
+      int vt = p.m - m0;
+      vt = vt > BM ? BM : vt;
+      T* cbase = reinterpret_cast<T*>(p.c);
+      const T* rbase = reinterpret_cast<const T*>(p.residual);
+#pragma unroll 1
+      for (int sub = 0; sub < NSUB; ++sub) {
+        const int n = nt * Cfg::BN + sub * 128 + qd * 32 + lane;
+        const bool nok = n < p.n;
+        T bias_v = Elem<T>::from_float(0.f), chan_s = Elem<T>::from_float(1.f);
+        if (nok && p.bias) bias_v = reinterpret_cast<const T*>(p.bias)[n];
+        if (!GROUPED && nok) chan_s = reinterpret_cast<const T*>(p.scales)[chan_scale_pos(n)];
+#pragma unroll 1
+        for (int c0 = 0; c0 < vt; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(qd * 32) << 16) + acc * Cfg::ACC_COLS +
+                            sub * BM + c0,
+                        v);
+          tmem_ld_wait();
+          if (nok) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int tok = m0 + c0 + i;
+              if (tok < p.m) {
+                T o = Elem<T>::from_float(__uint_as_float(v[i]));
+                if (!GROUPED) o = __hmul(o, chan_s);  // channelwise: scale the ROUNDED sum
+                const size_t off = static_cast<size_t>(tok) * p.n + n;
+                if (rbase) o = __hadd(rbase[off], o);
+                if (p.bias) o = __hadd(o, bias_v);
+                cbase[off] = o;
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_acc_empty + 8 * acc);
+    }
+  }
+
+  // teardown: every role is done with tensor memory before it is returned
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+}  // namespace b200

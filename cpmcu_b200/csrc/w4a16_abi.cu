@@ -139,21 +139,6 @@ int get_tensor_map(CUtensorMap* out, const void* ptr, CUtensorMapDataType type, 
 // ------------------------------------------------------------------------------------------
 // decode-regime configurations
 // ------------------------------------------------------------------------------------------
-struct GemmCall {
-  const void* a;
-  const int32_t* qweight;
-  const void* scales;
-  int32_t* workspace;
-  void* c;
-  float* c_tmp;
-  const void* bias;
-  const void* residual;
-  int m, n, k;       // m <= 8 * nt of the configuration
-  int group_size;
-  bool pdl;
-  cudaStream_t stream;
-};
-
 struct DecodeConfig {
   const char* name;
   int nt, chunks, krows, warps, stages;
@@ -276,6 +261,11 @@ int pick_geometry(int m, int n, int k) {
   return 2;
 }
 
+// configuration ids: 1..count = streaming-kernel configurations, kPrefillBase.. = tcgen05 tile shapes
+constexpr int kPrefillBase = 1001;
+// largest M served by the streaming kernel (in 32-token slabs); above it the tcgen05 kernel runs
+constexpr int kStreamMaxM = 64;
+
 struct Geom { int chunks, krows; };
 const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}};
 
@@ -308,6 +298,7 @@ int64_t b200_w4a16_workspace_ints(int64_t n) { return (n / 64) * 16; }
 
 int64_t b200_w4a16_reduce_bytes(int64_t m, int64_t n, int64_t k) {
   if (m <= 0 || n <= 0 || k <= 0 || n % 64 || k % 64) return -1;
+  if (m > kStreamMaxM) return 0;  // the tcgen05 kernel accumulates in tensor memory: no scratch
   const int rows = static_cast<int>(m < 32 ? m : 32);
   // worst case over the geometries the heuristic (or force_config) may use
   int64_t worst = 0;
@@ -324,12 +315,14 @@ int64_t b200_w4a16_reduce_bytes(int64_t m, int64_t n, int64_t k) {
 
 int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int dtype) {
   if (m <= 0 || n <= 0 || k <= 0 || (dtype != 0 && dtype != 1)) return -1;
+  if (m > kStreamMaxM) return kPrefillBase + prefill_pick_tile((int)m, (int)n, (int)k);
   const int mm = static_cast<int>(m < 32 ? m : 32);
   return 1 + decode_index(dtype, nt_for_m(mm), group_size != -1, pick_geometry(mm, (int)n, (int)k));
 }
 
 const char* b200_w4a16_config_name(int config) {
   const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
+  if (config >= kPrefillBase && config < kPrefillBase + kPrefillTiles) return prefill_tile_name(config - kPrefillBase);
   if (config < 1 || config > count) return "";
   return g_decode[config - 1].name;
 }
@@ -366,12 +359,6 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
       return fail(B200_W4A16_EINVAL, "group_size must not be -1 when has_act_order=true and is_k_full=true");
     if (!perm || !a_tmp) return fail(B200_W4A16_EINVAL, "has_act_order needs perm and a_tmp");
   }
-  if (!c_tmp) return fail(B200_W4A16_EINVAL, "c_tmp (fp32 reduce scratch) is required");
-  if (opts && opts->c_tmp_bytes > 0 && opts->c_tmp_bytes < b200_w4a16_reduce_bytes(m, n, k))
-    return fail(B200_W4A16_EINVAL, "c_tmp too small: %lld bytes given, %lld needed for MNK = [%lld, %lld, %lld]",
-                (long long)opts->c_tmp_bytes, (long long)b200_w4a16_reduce_bytes(m, n, k), (long long)m,
-                (long long)n, (long long)k);
-
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const size_t esz = 2;
   if (has_act_order) {
@@ -387,6 +374,37 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
 
   const bool grouped = group_size != -1;
   const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
+  const int forced = opts ? opts->force_config : 0;
+  // ---- tensor-bound regime: one persistent tcgen05 launch for any M ----
+  if ((forced == 0 && m > kStreamMaxM) || forced >= kPrefillBase) {
+    if (forced >= kPrefillBase + kPrefillTiles)
+      return fail(B200_W4A16_EINVAL, "force_config %d out of range", forced);
+    GemmCall g;
+    g.a = a;
+    g.qweight = qweight;
+    g.scales = scales;
+    g.workspace = workspace;
+    g.c = c;
+    g.c_tmp = c_tmp;
+    g.bias = opts ? opts->bias : nullptr;
+    g.residual = opts ? opts->residual : nullptr;
+    g.m = static_cast<int>(m);
+    g.n = static_cast<int>(n);
+    g.k = static_cast<int>(k);
+    g.group_size = group_size;
+    g.dtype = dtype;
+    g.pdl = opts ? (opts->pdl != 0) : (g_default_pdl.load(std::memory_order_relaxed) != 0);
+    g.stream = st;
+    return launch_prefill(g, forced ? forced - kPrefillBase : prefill_pick_tile(g.m, g.n, g.k));
+  }
+  // ---- streaming regime: needs the fp32 split-K scratch ----
+  {
+    const int64_t need = b200_w4a16_reduce_bytes(m < kStreamMaxM ? m : kStreamMaxM, n, k);
+    if (!c_tmp) return fail(B200_W4A16_EINVAL, "c_tmp (fp32 reduce scratch) is required");
+    if (opts && opts->c_tmp_bytes > 0 && opts->c_tmp_bytes < need)
+      return fail(B200_W4A16_EINVAL, "c_tmp too small: %lld bytes given, %lld needed for MNK = [%lld, %lld, %lld]",
+                  (long long)opts->c_tmp_bytes, (long long)need, (long long)m, (long long)n, (long long)k);
+  }
   // ---- M loop: slabs of <= 32 tokens through the streaming kernel ----
   for (int64_t m0 = 0; m0 < m; m0 += 32) {
     const int mm = static_cast<int>(m - m0 < 32 ? m - m0 : 32);
@@ -416,6 +434,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     g.n = static_cast<int>(n);
     g.k = static_cast<int>(k);
     g.group_size = group_size;
+    g.dtype = dtype;
     g.pdl = opts ? (opts->pdl != 0) : (g_default_pdl.load(std::memory_order_relaxed) != 0);
     g.stream = st;
     if (int rc = g_decode[idx].launch(g)) return rc;

@@ -1,0 +1,142 @@
+// Host side of the tcgen05 regime: tile-shape choice, TMA descriptors, launch.
+// (the reference's host logic for large M is the `par` M-loop of marlin_mm, gptq_marlin_mm.cu:161-206;
+//  here one persistent launch covers any M.)
+#include <cstring>
+
+#include "../../include/b200_w4a16.h"
+#include "host_common.h"
+#include "prefill_kernel.cuh"
+
+namespace b200 {
+
+namespace {
+
+struct TileShape {
+  int nsub, bm;
+  float weight;  // relative per-tile efficiency (bigger tiles amortise dequant + operand traffic)
+  const char* name;
+};
+const TileShape kTiles[kPrefillTiles] = {
+    {2, 256, 1.00f, "tc/bn256/bm256"},
+    {1, 256, 0.95f, "tc/bn128/bm256"},
+    {2, 128, 0.85f, "tc/bn256/bm128"},
+    {1, 128, 0.75f, "tc/bn128/bm128"},
+};
+
+template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED>
+int launch_one(const GemmCall& g) {
+  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED>;
+  auto kern = w4a16_prefill_kernel<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED>;
+  static bool attr_set = false;  // benign race: idempotent
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess)
+      return fail(B200_W4A16_ECUDA, "cudaFuncSetAttribute(smem=%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+    attr_set = true;
+  }
+  CUtensorMap tm_w, tm_s, tm_a;
+  {  // weights: int32 [K/16][N/64][128]; chunks past N/64 are zero-filled
+    const uint64_t dims[3] = {128, static_cast<uint64_t>(g.n / 64), static_cast<uint64_t>(g.k / 16)};
+    const uint64_t strides[2] = {512, static_cast<uint64_t>(g.n) * 8};
+    const uint32_t box[3] = {128, Cfg::CHUNKS, 4};
+    if (int rc = get_tensor_map(&tm_w, g.qweight, CU_TENSOR_MAP_DATA_TYPE_INT32, 3, dims, strides, box,
+                                CU_TENSOR_MAP_SWIZZLE_NONE))
+      return rc;
+  }
+  if (GROUPED) {  // scales: T [K/128][N/64][64]
+    const uint64_t dims[3] = {64, static_cast<uint64_t>(g.n / 64), static_cast<uint64_t>(g.k / 128)};
+    const uint64_t strides[2] = {128, static_cast<uint64_t>(g.n) * 2};
+    const uint32_t box[3] = {64, Cfg::CHUNKS, 1};
+    if (int rc = get_tensor_map(&tm_s, g.scales, Elem<T>::kTmaType, 3, dims, strides, box,
+                                CU_TENSOR_MAP_SWIZZLE_NONE))
+      return rc;
+  } else {
+    tm_s = tm_w;
+  }
+  {  // activations: T [M][K], [BM x 64] boxes, 128B swizzle, rows past M zero-filled
+    const uint64_t dims[2] = {static_cast<uint64_t>(g.k), static_cast<uint64_t>(g.m)};
+    const uint64_t strides[1] = {static_cast<uint64_t>(g.k) * 2};
+    const uint32_t box[2] = {64, BM};
+    if (int rc = get_tensor_map(&tm_a, g.a, Elem<T>::kTmaType, 2, dims, strides, box,
+                                CU_TENSOR_MAP_SWIZZLE_128B))
+      return rc;
+  }
+  PrefillArgs args;
+  args.c = g.c;
+  args.scales = g.scales;
+  args.bias = g.bias;
+  args.residual = g.residual;
+  args.m = g.m;
+  args.n = g.n;
+  args.k = g.k;
+  args.n_tiles = (g.n + Cfg::BN - 1) / Cfg::BN;
+  args.m_tiles = (g.m + BM - 1) / BM;
+  args.kblks = g.k / 64;
+  const long long tiles = static_cast<long long>(args.n_tiles) * args.m_tiles;
+  const int grid = static_cast<int>(tiles < sm_count() ? tiles : sm_count());
+
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(Cfg::THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = g.stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g.pdl ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tm_w, tm_s, tm_a, args);
+  if (e != cudaSuccess) return fail(B200_W4A16_ECUDA, "tcgen05 kernel launch: %s", cudaGetErrorString(e));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return 0;
+}
+
+template <typename T, bool GROUPED>
+int launch_tile(const GemmCall& g, int tile) {
+  switch (tile) {
+    case 0: return launch_one<T, 2, 256, 3, 3, 4, GROUPED>(g);
+    case 1: return launch_one<T, 1, 256, 4, 4, 4, GROUPED>(g);
+    case 2: return launch_one<T, 2, 128, 4, 3, 8, GROUPED>(g);
+    case 3: return launch_one<T, 1, 128, 6, 6, 4, GROUPED>(g);
+  }
+  return fail(B200_W4A16_EINVAL, "tcgen05 tile id %d out of range", tile);
+}
+
+}  // namespace
+
+const char* prefill_tile_name(int tile) {
+  return (tile >= 0 && tile < kPrefillTiles) ? kTiles[tile].name : "";
+}
+
+// widest tile whose wave quantisation on this device does not cost more than its size gains
+int prefill_pick_tile(int m, int n, int k) {
+  (void)k;
+  const int sms = sm_count();
+  int best = 0;
+  float best_score = -1.f;
+  for (int t = 0; t < kPrefillTiles; ++t) {
+    const int bn = kTiles[t].nsub * 128, bm = kTiles[t].bm;
+    const long long nt = (n + bn - 1) / bn, mt = (m + bm - 1) / bm, tiles = nt * mt;
+    const long long waves = (tiles + sms - 1) / sms;
+    // useful fraction of the issued MMA work: wave quantisation x padding of the last token / column tile
+    const float wave_eff = static_cast<float>(tiles) / static_cast<float>(waves * sms);
+    const float pad_eff = (static_cast<float>(m) / static_cast<float>(mt * bm)) *
+                          (static_cast<float>(n) / static_cast<float>(nt * bn));
+    const float score = wave_eff * pad_eff * kTiles[t].weight;
+    if (score > best_score) {
+      best_score = score;
+      best = t;
+    }
+  }
+  return best;
+}
+
+int launch_prefill(const GemmCall& g, int tile) {
+  const bool grouped = g.group_size != -1;
+  if (g.dtype == 0)
+    return grouped ? launch_tile<__half, true>(g, tile) : launch_tile<__half, false>(g, tile);
+  return grouped ? launch_tile<__nv_bfloat16, true>(g, tile) : launch_tile<__nv_bfloat16, false>(g, tile);
+}
+
+}  // namespace b200

@@ -95,6 +95,8 @@ SMALL = [  # (m, k, n): config 1 of BASELINE.json first, then ragged / edge shap
     (1, 4096, 4096), (1, 128, 64), (3, 256, 192), (4, 1024, 320), (8, 512, 1088), (10, 2048, 576),
     (12, 4096, 4608), (16, 1024, 2048), (17, 640, 448), (32, 1152, 1024), (33, 512, 512), (60, 768, 640),
     (64, 1024, 1024), (100, 256, 256),
+    # tcgen05 regime (M > 64): ragged token tiles, N not a multiple of the 128/256-column tile
+    (65, 128, 64), (128, 512, 384), (257, 256, 448), (354, 1024, 640), (513, 512, 1152),
 ]
 
 
@@ -118,7 +120,7 @@ def test_gemm_vs_oracle_and_reference(m, k, n, dtype):
     print(f"\n[m={m} k={k} n={n} dt={dtype}] vs exact: max_rel={st['max_rel']:.3e} mean_abs={st['mean_abs']:.3e}")
 
 
-@pytest.mark.parametrize("m,k,n", [(1, 1024, 512), (16, 2048, 1024), (40, 512, 256)])
+@pytest.mark.parametrize("m,k,n", [(1, 1024, 512), (16, 2048, 1024), (40, 512, 256), (130, 512, 320), (600, 256, 256)])
 @pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
 def test_gemm_channelwise(m, k, n, dtype):
     """group_size = -1: scale applied to the ROUNDED output (two roundings) — marlin_kernel_impl.cuh:957-963"""
@@ -156,6 +158,28 @@ def test_all_decode_configs_agree():
         assert st["max_rel"] <= TOL_MAX_REL, (name, st)
         seen += 1
     assert seen >= 4
+
+
+@pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
+def test_all_tcgen05_tiles_agree(dtype):
+    """every tile shape of the tcgen05 kernel (force_config 1001..) gives the oracle's answer, bit-identical
+    run to run, also when forced onto a small M (ragged token tile, UMMA N rounded up to 16)."""
+    from cpmcu_b200 import capi as L
+    for (m, k, n) in [(40, 256, 192), (300, 512, 448)]:
+        prob = mo.make_problem(m, k, n, 128, dtype, seed=m)
+        c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, dtype)
+        outs = []
+        for cfg in range(1001, 1005):
+            assert L.config_name(cfg).startswith("tc/")
+            out1, _ = run_ours(prob, m, n, k, dtype, force_config=cfg)
+            out2, _ = run_ours(prob, m, n, k, dtype, force_config=cfg)
+            assert torch.equal(out1, out2), f"{L.config_name(cfg)}: not deterministic"
+            st = mo.error_stats(t_load(out1, dtype), exact, dtype)
+            assert st["max_rel"] <= TOL_MAX_REL, (L.config_name(cfg), st)
+            outs.append(out1)
+        # same k order in every tile shape -> identical bits across shapes
+        for o in outs[1:]:
+            assert torch.equal(outs[0], o)
 
 
 def test_act_order_gather():
@@ -211,6 +235,33 @@ def test_linear_operator_postops():
     assert int(lin.workspace.abs().max()) == 0
 
 
+def test_linear_operator_postops_tcgen05():
+    """the same post-op contract on the tcgen05 path (M > 64)"""
+    b = _b()
+    m, k, n = 200, 256, 320
+    prob = mo.make_problem(m, k, n, 128, mo.FP16, seed=23)
+    rng = np.random.default_rng(5)
+    bias = rng.standard_normal(n).astype(np.float16)
+    tgt0 = rng.standard_normal((m, n)).astype(np.float16)
+    lin = b.W4A16GPTQMarlinLinear(k, n, 128, has_bias=True)
+    lin.init_weight_ptr()
+    lin.load_to_storage("x.qweight", torch.from_numpy(prob["qweight"]))
+    lin.load_to_storage("x.scales", torch.from_numpy(prob["scales_marlin"]))
+    lin.load_to_storage("x.bias", torch.from_numpy(bias))
+    a = torch.from_numpy(prob["a"]).to(DEV)
+    tgt = torch.from_numpy(tgt0).to(DEV)
+    lin.prefill(None, m, a, None, None, tgt=tgt, inplace=True)      # no c_tmp needed above M = 64
+    # the post-ops must be exactly the reference's rounding sequence applied to the kernel's own GEMM
+    # output: RN(RN(tgt + gemm) + bias), bit for bit (w4a16_gptq_marlin_linear.cuh:140-145)
+    ws, _ = scratch(m, n, k)
+    g = b.gemm(a, lin.weight, lin.scales, ws, None)
+    want = ((torch.from_numpy(tgt0).to(DEV) + g) + torch.from_numpy(bias).to(DEV))
+    assert torch.equal(tgt, want)
+    c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, mo.FP16)
+    st = mo.error_stats(g.cpu().numpy(), exact, mo.FP16)
+    assert st["max_rel"] <= TOL_MAX_REL, st
+
+
 def test_error_convention():
     b = _b()
     a = torch.zeros((1, 128), dtype=torch.float16, device=DEV)
@@ -226,6 +277,8 @@ def test_error_convention():
 
 FULL = [  # BASELINE.json config 2 shapes (MiniCPM4-8B) at tree-verify widths: ours vs reference Marlin
     (1, 4096, 4608), (4, 4096, 4096), (16, 4096, 32768), (64, 16384, 4096), (12, 4096, 32768), (60, 4096, 4608),
+    # BASELINE.json config 3: chunked prefill (tcgen05 path), incl. the ragged last chunk 106850 % 2048 = 354
+    (1024, 4096, 4608), (1024, 16384, 4096), (4096, 4096, 4096), (354, 4096, 32768), (2048, 4096, 32768),
 ]
 
 
