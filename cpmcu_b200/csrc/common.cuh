@@ -103,6 +103,16 @@ __device__ __forceinline__ void ldmatrix_x4(uint32_t& r0, uint32_t& r1, uint32_t
                : "r"(addr));
 }
 
+// 16-byte shared-memory load by 32-bit shared address (keeps the access an LDS: pointers derived
+// from the manually aligned dynamic-smem base are generic to the compiler)
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(addr));
+  return v;
+}
+
 // four 8x8 b16 matrices, register i of every lane -> matrix i, row addresses from lanes 8i..8i+7
 __device__ __forceinline__ void stmatrix_x4(uint32_t addr, uint32_t r0, uint32_t r1, uint32_t r2,
                                             uint32_t r3) {

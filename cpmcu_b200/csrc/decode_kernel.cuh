@@ -186,21 +186,20 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
 
     uint32_t s_lo[4], s_hi[4];
     if (GROUPED) {
-      const uint4 sv = *reinterpret_cast<const uint4*>(smem + Cfg::OFF_S + s * Cfg::S_STAGE +
-                                                       wn * 128 + g * 16);
+      const uint4 sv = lds128(sbase + Cfg::OFF_S + s * Cfg::S_STAGE + wn * 128 + g * 16);
       broadcast_scale_pair(sv.x, s_lo[0], s_hi[0]);
       broadcast_scale_pair(sv.y, s_lo[1], s_hi[1]);
       broadcast_scale_pair(sv.z, s_lo[2], s_hi[2]);
       broadcast_scale_pair(sv.w, s_lo[3], s_hi[3]);
     }
-    const uint8_t* wst = smem + Cfg::OFF_W + s * Cfg::W_STAGE;
+    const uint32_t wst = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
     const uint32_t ast = sbase + Cfg::OFF_A + s * Cfg::A_STAGE;
 
     uint4 q[RPW];
 #pragma unroll
     for (int i = 0; i < RPW; ++i) {
       const int r = wk + WK * i;
-      q[i] = *reinterpret_cast<const uint4*>(wst + (r * CHUNKS + wn) * 512 + lane * 16);
+      q[i] = lds128(wst + (r * CHUNKS + wn) * 512 + lane * 16);
     }
 #pragma unroll
     for (int i = 0; i < RPW; ++i) {

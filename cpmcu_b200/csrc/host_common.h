@@ -40,6 +40,12 @@ int prefill_pick_tile(int m, int n, int k);
 const char* prefill_tile_name(int tile);
 int launch_prefill(const GemmCall& g, int tile);
 
+// defined in w4a16_stream.cu: the cluster split-K streaming regime (g.m <= 32)
+constexpr int kStreamGeoms = 6;
+void stream_pick(const GemmCall& g, int* geom, int* S);
+const char* stream_geom_name(int geom);
+int launch_stream(const GemmCall& g, int geom, int S);
+
 // Upper bound on the number of CTAs whose unit ranges intersect one column of `kblks` units when
 // `units` units are split evenly over `grid` CTAs (every CTA gets floor or ceil of units/grid):
 // one partial run at each end plus the whole runs between them.  This is the per-column slot

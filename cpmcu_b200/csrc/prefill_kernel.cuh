@@ -192,8 +192,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
         mbar_wait(bar_q_full + 8 * sq, (it / QSTAGES) & 1);
         uint32_t s_lo[4] = {0, 0, 0, 0}, s_hi[4] = {0, 0, 0, 0};
         if (GROUPED) {
-          const uint4 sv = *reinterpret_cast<const uint4*>(smem + Cfg::OFF_S + sq * Cfg::S_STAGE +
-                                                           ch * 128 + g * 16);
+          const uint4 sv = lds128(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE + ch * 128 + g * 16);
           broadcast_scale_pair(sv.x, s_lo[0], s_hi[0]);
           broadcast_scale_pair(sv.y, s_lo[1], s_hi[1]);
           broadcast_scale_pair(sv.z, s_lo[2], s_hi[2]);
@@ -203,8 +202,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
         for (int i = 0; i < Cfg::RPW; ++i) {
           const int r = rp + Cfg::WPC * i;
-          q[i] = *reinterpret_cast<const uint4*>(smem + Cfg::OFF_Q + sq * Cfg::Q_STAGE +
-                                                 (r * CHUNKS + ch) * 512 + lane * 16);
+          q[i] = lds128(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE + (r * CHUNKS + ch) * 512 + lane * 16);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);  // raw slot is in registers now

@@ -29,6 +29,20 @@ std::atomic<int> g_default_pdl{[] {
   return (e && e[0] == '1') ? 1 : 0;
 }()};
 
+// which streaming kernel serves M <= 64 by default: 1 = cluster split-K (stream_kernel.cuh),
+// 0 = first generation (decode_kernel.cuh); environment B200_W4A16_STREAM_V2 overrides
+bool g_stream_v2 = [] {
+  const char* e = std::getenv("B200_W4A16_STREAM_V2");
+  return e ? (e[0] == '1') : true;
+}();
+
+// cap on resident CTAs per SM of the first-generation persistent streaming kernel
+int g_v1_occ = [] {
+  const char* e = std::getenv("B200_W4A16_V1_OCC");
+  const int v = e ? std::atoi(e) : 1;
+  return v < 1 ? 1 : (v > 4 ? 4 : v);
+}();
+
 int fail(int code, const char* fmt, ...) {
   char buf[1024];
   va_list ap;
@@ -199,7 +213,15 @@ int launch_decode(const GemmCall& g) {
   args.ncols = (g.n + Cfg::TN - 1) / Cfg::TN;
   args.kblks = g.k / Cfg::KB;
   const long long units = static_cast<long long>(args.ncols) * args.kblks;
-  const int grid = static_cast<int>(units < sm_count() ? units : sm_count());
+  // persistent CTAs: as many per SM as shared memory / registers allow (capped by B200_W4A16_V1_OCC)
+  static int occ = 0;
+  if (occ == 0) {
+    int o = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, Cfg::THREADS, Cfg::SMEM_BYTES) != cudaSuccess || o < 1) o = 1;
+    occ = o < g_v1_occ ? o : g_v1_occ;
+  }
+  const long long slots = static_cast<long long>(sm_count()) * occ;
+  const int grid = static_cast<int>(units < slots ? units : slots);
   args.slot_max = decode_slot_max(args.kblks, units, grid);
 
   cudaLaunchConfig_t cfg;
@@ -263,6 +285,8 @@ int pick_geometry(int m, int n, int k) {
 
 // configuration ids: 1..count = streaming-kernel configurations, kPrefillBase.. = tcgen05 tile shapes
 constexpr int kPrefillBase = 1001;
+// cluster split-K streaming kernel: id = kStreamBase + geometry * 4 + log2(cluster size)
+constexpr int kStreamBase = 2001;
 // largest M served by the streaming kernel (in 32-token slabs); above it the tcgen05 kernel runs
 constexpr int kStreamMaxM = 64;
 
@@ -306,6 +330,13 @@ int64_t b200_w4a16_reduce_bytes(int64_t m, int64_t n, int64_t k) {
     const int tn = kGeom[geo].chunks * 64, kb = kGeom[geo].krows * 16;
     if (k % kb) continue;
     const long long ncols = (n + tn - 1) / tn, kblks = k / kb, units = ncols * kblks;
+    // worst case over the occupancies launch_decode may pick (1 .. g_v1_occ CTAs per SM)
+    for (int occ = 1; occ <= g_v1_occ; ++occ) {
+      const long long slots = static_cast<long long>(sm_count()) * occ;
+      const int grid = static_cast<int>(units < slots ? units : slots);
+      const int64_t b2 = ncols * decode_slot_max(static_cast<int>(kblks), units, grid) * rows * tn * 4ll;
+      if (b2 > worst) worst = b2;
+    }
     const int grid = static_cast<int>(units < sm_count() ? units : sm_count());
     const int64_t bytes = ncols * decode_slot_max(static_cast<int>(kblks), units, grid) * rows * tn * 4ll;
     if (bytes > worst) worst = bytes;
@@ -317,12 +348,26 @@ int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int 
   if (m <= 0 || n <= 0 || k <= 0 || (dtype != 0 && dtype != 1)) return -1;
   if (m > kStreamMaxM) return kPrefillBase + prefill_pick_tile((int)m, (int)n, (int)k);
   const int mm = static_cast<int>(m < 32 ? m : 32);
+  if (g_stream_v2) {
+    GemmCall g;
+    std::memset(&g, 0, sizeof(g));
+    g.m = mm;
+    g.n = static_cast<int>(n);
+    g.k = static_cast<int>(k);
+    g.group_size = group_size;
+    g.dtype = dtype;
+    int geom = 0, S = 1, l2 = 0;
+    stream_pick(g, &geom, &S);
+    while ((1 << l2) < S) ++l2;
+    return kStreamBase + geom * 4 + l2;
+  }
   return 1 + decode_index(dtype, nt_for_m(mm), group_size != -1, pick_geometry(mm, (int)n, (int)k));
 }
 
 const char* b200_w4a16_config_name(int config) {
   const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
   if (config >= kPrefillBase && config < kPrefillBase + kPrefillTiles) return prefill_tile_name(config - kPrefillBase);
+  if (config >= kStreamBase && config < kStreamBase + kStreamGeoms * 4) return stream_geom_name((config - kStreamBase) >> 2);
   if (config < 1 || config > count) return "";
   return g_decode[config - 1].name;
 }
@@ -376,7 +421,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
   const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
   const int forced = opts ? opts->force_config : 0;
   // ---- tensor-bound regime: one persistent tcgen05 launch for any M ----
-  if ((forced == 0 && m > kStreamMaxM) || forced >= kPrefillBase) {
+  if ((forced == 0 && m > kStreamMaxM) || (forced >= kPrefillBase && forced < kStreamBase)) {
     if (forced >= kPrefillBase + kPrefillTiles)
       return fail(B200_W4A16_EINVAL, "force_config %d out of range", forced);
     GemmCall g;
@@ -408,8 +453,10 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
   // ---- M loop: slabs of <= 32 tokens through the streaming kernel ----
   for (int64_t m0 = 0; m0 < m; m0 += 32) {
     const int mm = static_cast<int>(m - m0 < 32 ? m - m0 : 32);
-    int idx;
-    if (opts && opts->force_config > 0) {
+    int idx = -1;
+    if (forced >= kStreamBase || (forced == 0 && g_stream_v2)) {
+      // cluster split-K streaming kernel
+    } else if (opts && opts->force_config > 0) {
       idx = opts->force_config - 1;
       if (idx >= count) return fail(B200_W4A16_EINVAL, "force_config %d out of range", opts->force_config);
       const DecodeConfig& f = g_decode[idx];
@@ -437,6 +484,18 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     g.dtype = dtype;
     g.pdl = opts ? (opts->pdl != 0) : (g_default_pdl.load(std::memory_order_relaxed) != 0);
     g.stream = st;
+    if (idx < 0) {
+      int geom, S;
+      if (forced >= kStreamBase) {
+        geom = (forced - kStreamBase) >> 2;
+        S = 1 << ((forced - kStreamBase) & 3);
+        if (geom >= kStreamGeoms) return fail(B200_W4A16_EINVAL, "force_config %d out of range", forced);
+      } else {
+        stream_pick(g, &geom, &S);
+      }
+      if (int rc = launch_stream(g, geom, S)) return rc;
+      continue;
+    }
     if (int rc = g_decode[idx].launch(g)) return rc;
   }
   return B200_W4A16_OK;

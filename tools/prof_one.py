@@ -1,0 +1,33 @@
+#!/usr/bin/env python
+"""Launch one (shape, M, config) a few times over rotating weight copies — the command ncu wraps.
+  python tools/prof_one.py --k 4096 --n 32768 --m 1 --cfg 2010 [--copies 6] [--pdl]"""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+import cpmcu_b200 as B  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--k", type=int, default=4096)
+ap.add_argument("--n", type=int, default=32768)
+ap.add_argument("--m", type=int, default=1)
+ap.add_argument("--cfg", type=int, default=0)
+ap.add_argument("--copies", type=int, default=6)
+ap.add_argument("--pdl", action="store_true")
+a_ = ap.parse_args()
+dev = "cuda"
+k, n, m = a_.k, a_.n, a_.m
+qw = torch.randint(-2**31, 2**31 - 1, (a_.copies, k // 16, 2 * n), dtype=torch.int32, device=dev)
+sc = (torch.rand((a_.copies, k // 128, n), device=dev) * 0.018 + 0.002).half()
+a = torch.randn((m, k), device=dev).half()
+out = torch.empty((m, n), dtype=torch.float16, device=dev)
+ws = torch.zeros(B.workspace_ints(n), dtype=torch.int32, device=dev)
+ct = torch.empty(max(B.reduce_bytes(m, n, k) // 4, 64), dtype=torch.float32, device=dev)
+for rep in range(2):
+    for i in range(a_.copies):
+        B.gemm(a, qw[i], sc[i], ws, ct, out=out, force_config=a_.cfg, pdl=a_.pdl)
+torch.cuda.synchronize()
+print("done", B.launch_count())

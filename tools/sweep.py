@@ -49,6 +49,8 @@ def main():
     ap.add_argument("--ms", default="1,4,16")
     ap.add_argument("--shapes", default="qkv,o,gate_up,down")
     ap.add_argument("--geoms", default="all")
+    ap.add_argument("--family", default="both", choices=["v1", "v2", "both"])
+    ap.add_argument("--pdl-only", action="store_true")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))
     args = ap.parse_args()
     dev = "cuda"
@@ -76,14 +78,22 @@ def main():
                 results.append(r)
                 print(json.dumps(r), flush=True)
             default_cfg = L.pick_config(m, n, k)
-            for cfg in range(1, 400):
-                cname = L.config_name(cfg)
-                if not cname:
-                    break
-                nt = 1 if m <= 8 else (2 if m <= 16 else 4)
-                if not cname.startswith(f"__half/nt{nt}/") or not cname.endswith("true"):
-                    continue
-                for pdl in (False, True):
+            cands = []
+            nt = 1 if m <= 8 else (2 if m <= 16 else 4)
+            if args.family in ("v1", "both"):
+                for cfg in range(1, 400):
+                    cname = L.config_name(cfg)
+                    if not cname:
+                        break
+                    if cname.startswith(f"__half/nt{nt}/") and cname.endswith("true"):
+                        cands.append((cfg, cname))
+            if args.family in ("v2", "both"):
+                for cfg in range(2001, 2001 + 64):
+                    cname = L.config_name(cfg)
+                    if cname:
+                        cands.append((cfg, f"{cname}/S{1 << ((cfg - 2001) & 3)}"))
+            for cfg, cname in cands:
+                for pdl in ((True,) if args.pdl_only else (False, True)):
                     def run():
                         for i in range(copies):
                             B.gemm(a, qw[i], sc[i], ws, ct, out=out, force_config=cfg, pdl=pdl)
