@@ -59,6 +59,7 @@ SYMBOLS = {
     "b200_w4a16_set_pdl": (c_int, [c_int]),
     "b200_w4a16_pick_config": (c_int, [c_int64, c_int64, c_int64, c_int, c_int]),
     "b200_w4a16_config_name": (c_char_p, [c_int]),
+    "b200_w4a16_max_clusters": (c_int, [c_int, c_int64, c_int, c_int]),
     "b200_w4a16_last_error": (c_char_p, []),
     "b200_w4a16_version": (c_char_p, []),
 }

@@ -35,16 +35,19 @@ int get_tensor_map(CUtensorMap* out, const void* ptr, CUtensorMapDataType type, 
                    CUtensorMapSwizzle swz);
 
 // defined in w4a16_prefill.cu: the tcgen05 regime
-constexpr int kPrefillTiles = 4;  // (NSUB,BM) = (2,256) (1,256) (2,128) (1,128)
-int prefill_pick_tile(int m, int n, int k);
+constexpr int kPrefillTiles = 6;  // (NSUB,BM) = (2,256) (1,256) (2,128) (1,128); split-K (1,64) (1,128)
+constexpr int kPrefillWholeK = 4; // tiles below this index are whole-K (persistent); the rest are split-K
+void prefill_pick(const GemmCall& g, int* tile, int* S);
 const char* prefill_tile_name(int tile);
-int launch_prefill(const GemmCall& g, int tile);
+int launch_prefill(const GemmCall& g, int tile, int S);
+int prefill_max_clusters(const GemmCall& g, int tile, int S);
 
 // defined in w4a16_stream.cu: the cluster split-K streaming regime (g.m <= 32)
 constexpr int kStreamGeoms = 6;
 void stream_pick(const GemmCall& g, int* geom, int* S);
 const char* stream_geom_name(int geom);
 int launch_stream(const GemmCall& g, int geom, int S);
+int stream_max_clusters(const GemmCall& g, int geom, int S);
 
 // Upper bound on the number of CTAs whose unit ranges intersect one column of `kblks` units when
 // `units` units are split evenly over `grid` CTAs (every CTA gets floor or ceil of units/grid):

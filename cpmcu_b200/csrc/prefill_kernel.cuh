@@ -4,9 +4,10 @@
 // and the TOKENS are the UMMA "B" operand (N side, up to 256 per instruction), so one dequantised
 // tile feeds 128 x BM x 64 MACs and the accumulator D^T[n][token] lives in tensor memory.
 //
-//   warp 4      TMA producer: raw Marlin int4 boxes + group scales (ring Q), activation boxes
-//               [BM tokens x 64 k], 128B-swizzled, rows past M zero-filled (ring A)
-//   warps 6..   dequantisers: LDS.128 of a lane's 16 B -> lop3/HSUB2/HFMA2 (exact) -> HMUL2 by the
+//   warp 6      TMA producer: raw Marlin int4 boxes + group scales (ring Q, deep: the HBM stream)
+//   warp 4      TMA producer: activation boxes [BM tokens x 64 k], 128B-swizzled, rows past M
+//               zero-filled (ring A)
+//   warps 7..   dequantisers: LDS.128 of a lane's 16 B -> lop3/HSUB2/HFMA2 (exact) -> HMUL2 by the
 //               group scale (the reference's single rounding point, marlin_device_ops.cuh:294-303)
 //               -> stmatrix.x4 straight into the canonical K-major SWIZZLE_128B UMMA layout: the
 //               Marlin fragment order IS the stmatrix 8x8 fragment order, so a 32-bit word of the
@@ -29,9 +30,10 @@ struct PrefillArgs {
   const void* residual;  // T[M][N] or null (may alias c)
   int m, n, k;
   int n_tiles, m_tiles, kblks;
+  int dbg;  // tuning only: bit0 = dequantisers skip the conversion, bit1 = MMA issuer skips the MMAs
 };
 
-template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED>
+template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT = false>
 struct PrefillCfg {
   static constexpr int BN = NSUB * 128;            // output columns per CTA tile
   static constexpr int CHUNKS = NSUB * 2;          // 64-column Marlin chunks per tile
@@ -41,8 +43,12 @@ struct PrefillCfg {
   static constexpr int Q_STAGE = 4 * CHUNKS * 512; // raw int4: 4 k16-rows x CHUNKS blocks of 512 B
   static constexpr int S_STAGE = GROUPED ? BN * 2 : 0;
   static constexpr int ACC_COLS = NSUB * BM;       // fp32 TMEM columns per accumulator
-  static constexpr int ACC_STAGES = (512 / ACC_COLS) >= 2 ? 2 : 1;
-  static constexpr int TMEM_COLS = ACC_COLS * ACC_STAGES;  // 256 or 512: a power of two
+  static constexpr int ACC_STAGES = (!SPLIT && (512 / ACC_COLS) >= 2) ? 2 : 1;
+  static constexpr int TMEM_COLS = ACC_COLS * ACC_STAGES;  // a power of two >= 32
+  // split-K: fp32 partial tile [BM tokens][128 + 4] staged for the cluster reduction; it aliases the
+  // A/W rings, which are dead once the last MMA of the CTA's only tile has been committed
+  static constexpr int RED_PITCH = 128 + 4;
+  static constexpr int RED_BYTES = SPLIT ? BM * RED_PITCH * 4 : 0;
   static constexpr int WPC = DW / CHUNKS;          // dequant warps sharing a chunk
   static constexpr int RPW = 4 / WPC;              // k16-rows per dequant warp per stage
   static constexpr int OFF_A = 0;
@@ -52,18 +58,19 @@ struct PrefillCfg {
   static constexpr int OFF_BAR = (OFF_S + QSTAGES * S_STAGE + 127) / 128 * 128;
   static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4;
   static constexpr int SMEM_BYTES = OFF_BAR + NBARS * 8 + 16 + 1024;  // +1024: manual alignment
-  static constexpr int THREADS = (6 + DW) * 32;
+  static constexpr int THREADS = (7 + DW) * 32;
   static_assert(DW % CHUNKS == 0 && WPC >= 1 && 4 % WPC == 0, "dequant warp layout");
-  static_assert(TMEM_COLS == 256 || TMEM_COLS == 512, "tensor memory allocation");
+  static_assert(TMEM_COLS >= 32 && TMEM_COLS <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "tensor memory allocation");
+  static_assert(!SPLIT || (NSUB == 1 && RED_BYTES <= OFF_BAR), "split-K staging must fit in the dead rings (A, W and Q are all drained when the accumulator is complete)");
   static_assert(BM % 16 == 0 && BM <= 256, "UMMA N");
   static_assert(SMEM_BYTES <= 232448, "shared memory budget (227 KB)");
 };
 
-template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED>
-__global__ void __launch_bounds__((6 + DW) * 32, 1)
+template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT>
+__global__ void __launch_bounds__((7 + DW) * 32, SPLIT ? 2 : 1)
 w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_s,
                      const __grid_constant__ CUtensorMap tm_a, const PrefillArgs p) {
-  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED>;
+  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
   constexpr int CHUNKS = Cfg::CHUNKS;
 
   extern __shared__ uint8_t smem_raw[];
@@ -112,37 +119,61 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
   pdl_wait_prior_grids();
 
   const int total_tiles = p.n_tiles * p.m_tiles;
+  // work items: persistent walk over whole-K tiles, or (split-K) exactly one tile and one K slice
+  // per CTA, the S CTAs of a cluster sharing the tile
+  int tile_begin = blockIdx.x, tile_step = gridDim.x, kb_lo = 0, kb_hi = p.kblks;
+  int csize = 1, crank = 0;
+  if (SPLIT) {
+    csize = static_cast<int>(cluster_nctarank());
+    crank = static_cast<int>(cluster_ctarank());
+    tile_begin = blockIdx.x / csize;
+    tile_step = total_tiles;
+    kb_lo = static_cast<int>((static_cast<long long>(crank) * p.kblks) / csize);
+    kb_hi = static_cast<int>((static_cast<long long>(crank + 1) * p.kblks) / csize);
+  }
 
   if (warp == 4) {
-    // ===================================== TMA producer =====================================
+    // ============================== TMA producer: activations (ring A) ==============================
     if (lane == 0) {
-      tma_prefetch_desc(&tm_w);
       tma_prefetch_desc(&tm_a);
-      if (GROUPED) tma_prefetch_desc(&tm_s);
       int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int mt = tile % p.m_tiles, nt = tile / p.m_tiles;
-        for (int kb = 0; kb < p.kblks; ++kb, ++it) {
-          const int sq = it % QSTAGES;
-          mbar_wait(bar_q_empty + 8 * sq, ((it / QSTAGES) & 1) ^ 1);
-          mbar_arrive_expect_tx(bar_q_full + 8 * sq, Cfg::Q_STAGE + Cfg::S_STAGE);
-          tma_load_3d(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE, &tm_w, bar_q_full + 8 * sq, 0, nt * CHUNKS,
-                      kb * 4, kEvictNormal);
-          if (GROUPED)
-            tma_load_3d(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE, &tm_s, bar_q_full + 8 * sq, 0,
-                        nt * CHUNKS, kb >> 1, kEvictLast);
+      for (int tile = tile_begin; tile < total_tiles; tile += tile_step) {
+        const int mt = tile % p.m_tiles;
+        for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
           const int s = it % STAGES;
-          mbar_wait(bar_consumed + 8 * s, ((it / STAGES) & 1) ^ 1);
+          mbar_wait_backoff(bar_consumed + 8 * s, ((it / STAGES) & 1) ^ 1, 32);
           mbar_arrive_expect_tx(bar_a_full + 8 * s, Cfg::A_STAGE);
           tma_load_2d(sbase + Cfg::OFF_A + s * Cfg::A_STAGE, &tm_a, bar_a_full + 8 * s, kb * 64, mt * BM,
                       kEvictLast);
         }
       }
     }
+  } else if (warp == 6) {
+    // ===================== TMA producer: raw int4 weights + group scales (ring Q) =====================
+    // its own lane and its own, deeper ring: the HBM stream runs QSTAGES boxes ahead of the dequantisers
+    // independently of the activation / tensor-core pipeline
+    if (lane == 0) {
+      tma_prefetch_desc(&tm_w);
+      if (GROUPED) tma_prefetch_desc(&tm_s);
+      int it = 0;
+      for (int tile = tile_begin; tile < total_tiles; tile += tile_step) {
+        const int nt = tile / p.m_tiles;
+        for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
+          const int sq = it % QSTAGES;
+          mbar_wait_backoff(bar_q_empty + 8 * sq, ((it / QSTAGES) & 1) ^ 1, 32);
+          mbar_arrive_expect_tx(bar_q_full + 8 * sq, Cfg::Q_STAGE + Cfg::S_STAGE);
+          tma_load_3d(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE, &tm_w, bar_q_full + 8 * sq, 0, nt * CHUNKS,
+                      kb * 4, SPLIT ? kEvictFirst : kEvictNormal);
+          if (GROUPED)
+            tma_load_3d(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE, &tm_s, bar_q_full + 8 * sq, 0,
+                        nt * CHUNKS, kb >> 1, kEvictLast);
+        }
+      }
+    }
   } else if (warp == 5) {
     // ======================================= MMA issuer =======================================
     int it = 0, acc_it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++acc_it) {
+    for (int tile = tile_begin; tile < total_tiles; tile += tile_step, ++acc_it) {
       const int mt = tile % p.m_tiles;
       const int acc = acc_it % Cfg::ACC_STAGES;
       mbar_wait(bar_acc_empty + 8 * acc, ((acc_it / Cfg::ACC_STAGES) & 1) ^ 1);
@@ -151,7 +182,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       vt = vt > BM ? BM : vt;
       const uint32_t idesc = umma_idesc_f16<T>(128, static_cast<uint32_t>((vt + 15) & ~15));
       const uint32_t d0 = tmem_base + acc * Cfg::ACC_COLS;
-      for (int kb = 0; kb < p.kblks; ++kb, ++it) {
+      for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
         const int s = it % STAGES;
         const uint32_t ph = (it / STAGES) & 1;
         mbar_wait(bar_a_full + 8 * s, ph);
@@ -166,18 +197,18 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
             for (int kk = 0; kk < 4; ++kk) {
               const uint64_t adesc = umma_desc_k_sw128(w_addr + sub * 16384 + kk * 32);
               const uint64_t bdesc = umma_desc_k_sw128(a_addr + kk * 32);
-              tc_mma_f16(d0 + sub * BM, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+              if (!(p.dbg & 2)) tc_mma_f16(d0 + sub * BM, adesc, bdesc, idesc, (kb != kb_lo || kk != 0) ? 1u : 0u);
             }
           }
           tc_commit(bar_consumed + 8 * s);
-          if (kb == p.kblks - 1) tc_commit(bar_acc_full + 8 * acc);
+          if (kb == kb_hi - 1) tc_commit(bar_acc_full + 8 * acc);
         }
         __syncwarp();
       }
     }
-  } else if (warp >= 6) {
+  } else if (warp >= 7) {
     // ====================================== dequantisers ======================================
-    const int d = warp - 6;
+    const int d = warp - 7;
     const int ch = d % CHUNKS;      // 64-column chunk of the tile
     const int rp = d / CHUNKS;      // k16-row phase
     const int g = lane >> 2;
@@ -186,8 +217,8 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
     const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8;
     const int lkh = lane >> 4;
     int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      for (int kb = 0; kb < p.kblks; ++kb, ++it) {
+    for (int tile = tile_begin; tile < total_tiles; tile += tile_step) {
+      for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
         const int sq = it % QSTAGES;
         mbar_wait(bar_q_full + 8 * sq, (it / QSTAGES) & 1);
         uint32_t s_lo[4] = {0, 0, 0, 0}, s_hi[4] = {0, 0, 0, 0};
@@ -210,6 +241,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
         const int s = it % STAGES;
         mbar_wait(bar_consumed + 8 * s, ((it / STAGES) & 1) ^ 1);  // W slot drained by the tensor core
         const uint32_t w_addr = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
+        if (!(p.dbg & 1))
 #pragma unroll
         for (int i = 0; i < Cfg::RPW; ++i) {
           const int r = rp + Cfg::WPC * i;
@@ -235,10 +267,10 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
     // ======================================== epilogue ========================================
     const int qd = warp;  // TMEM lane quarter: this warp may touch lanes 32*qd .. 32*qd+31
     int acc_it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++acc_it) {
+    for (int tile = tile_begin; tile < total_tiles; tile += tile_step, ++acc_it) {
       const int mt = tile % p.m_tiles, nt = tile / p.m_tiles;
       const int acc = acc_it % Cfg::ACC_STAGES;
-      mbar_wait(bar_acc_full + 8 * acc, (acc_it / Cfg::ACC_STAGES) & 1);
+      mbar_wait_backoff(bar_acc_full + 8 * acc, (acc_it / Cfg::ACC_STAGES) & 1, 256);
       tc_fence_after();
       const int m0 = mt * BM;
       int vt = p.m - m0;
@@ -259,7 +291,13 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
                             sub * BM + c0,
                         v);
           tmem_ld_wait();
-          if (nok) {
+          if (SPLIT) {
+            // fp32 partial -> staging tile [token][n]; lanes write consecutive n: conflict-free
+            float* red = reinterpret_cast<float*>(smem + Cfg::OFF_A);
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              red[(c0 + i) * Cfg::RED_PITCH + qd * 32 + lane] = __uint_as_float(v[i]);
+          } else if (nok) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
               const int tok = m0 + c0 + i;
@@ -279,6 +317,60 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_acc_empty + 8 * acc);
     }
+  }
+
+  if (SPLIT) {
+    // ---- cluster reduction over the K slices, in rank order (bit-deterministic) ----
+    cluster_sync_all();
+    if (tile_begin < total_tiles && warp < 4) {
+      const int mt = tile_begin % p.m_tiles, nt = tile_begin / p.m_tiles;
+      const int m0 = mt * BM;
+      int vt = p.m - m0;
+      vt = vt > BM ? BM : vt;
+      const int total = vt * 32;  // float4 items of the valid rows
+      const int e0 = static_cast<int>((static_cast<long long>(crank) * total) / csize);
+      const int e1 = static_cast<int>((static_cast<long long>(crank + 1) * total) / csize);
+      const uint32_t red_addr = sbase + Cfg::OFF_A;
+      for (int e = e0 + static_cast<int>(threadIdx.x); e < e1; e += 128) {
+        const int tok = e >> 5, nn = (e & 31) * 4;
+        const uint32_t off = static_cast<uint32_t>(tok * Cfg::RED_PITCH + nn) * 4u;
+        float4 sum = ld_dsmem_f4(red_addr + off, 0);
+        for (int r = 1; r < csize; ++r) {
+          const float4 v = ld_dsmem_f4(red_addr + off, static_cast<uint32_t>(r));
+          sum.x += v.x;
+          sum.y += v.y;
+          sum.z += v.z;
+          sum.w += v.w;
+        }
+        const int n = nt * Cfg::BN + nn;
+        if (n >= p.n) continue;
+        T o[4] = {Elem<T>::from_float(sum.x), Elem<T>::from_float(sum.y), Elem<T>::from_float(sum.z),
+                  Elem<T>::from_float(sum.w)};
+        if (!GROUPED) {
+          const T* sc = reinterpret_cast<const T*>(p.scales);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) o[i] = __hmul(o[i], sc[chan_scale_pos(n + i)]);
+        }
+        const size_t goff = static_cast<size_t>(m0 + tok) * p.n + n;
+        if (p.residual) {
+          const T* rs = reinterpret_cast<const T*>(p.residual) + goff;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) o[i] = __hadd(rs[i], o[i]);
+        }
+        if (p.bias) {
+          const T* bs = reinterpret_cast<const T*>(p.bias) + n;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) o[i] = __hadd(o[i], bs[i]);
+        }
+        uint2 pk;
+        pk.x = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[0])) |
+               (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[1])) << 16);
+        pk.y = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[2])) |
+               (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[3])) << 16);
+        *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.c) + goff) = pk;
+      }
+    }
+    cluster_sync_all();  // no CTA exits while a peer may still read its staging tile
   }
 
   // teardown: every role is done with tensor memory before it is returned

@@ -287,8 +287,32 @@ int pick_geometry(int m, int n, int k) {
 constexpr int kPrefillBase = 1001;
 // cluster split-K streaming kernel: id = kStreamBase + geometry * 4 + log2(cluster size)
 constexpr int kStreamBase = 2001;
-// largest M served by the streaming kernel (in 32-token slabs); above it the tcgen05 kernel runs
-constexpr int kStreamMaxM = 64;
+// largest M served by the streaming kernel; above it the tcgen05 kernel runs (split-K clusters up to
+// M = 256, persistent whole-K tiles beyond).  Measured crossover on B200: profiles/r01 sweep_mid.
+int kStreamMaxM = [] {
+  const char* e = std::getenv("B200_W4A16_STREAM_MAX_M");
+  const int v = e ? std::atoi(e) : 32;
+  return v < 0 ? 0 : v;
+}();
+// tcgen05 ids: kPrefillBase + t (whole-K tiles, t < kPrefillWholeK), then
+// kPrefillBase + kPrefillWholeK + (t - kPrefillWholeK) * 4 + log2(cluster size) for the split-K tiles
+constexpr int kPrefillIds = kPrefillWholeK + (kPrefillTiles - kPrefillWholeK) * 4;
+int prefill_id(int tile, int S) {
+  if (tile < kPrefillWholeK) return kPrefillBase + tile;
+  int l2 = 0;
+  while ((1 << l2) < S) ++l2;
+  return kPrefillBase + kPrefillWholeK + (tile - kPrefillWholeK) * 4 + l2;
+}
+void prefill_from_id(int id, int* tile, int* S) {
+  const int r = id - kPrefillBase;
+  if (r < kPrefillWholeK) {
+    *tile = r;
+    *S = 1;
+  } else {
+    *tile = kPrefillWholeK + (r - kPrefillWholeK) / 4;
+    *S = 1 << ((r - kPrefillWholeK) & 3);
+  }
+}
 
 struct Geom { int chunks, krows; };
 const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}};
@@ -346,7 +370,18 @@ int64_t b200_w4a16_reduce_bytes(int64_t m, int64_t n, int64_t k) {
 
 int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int dtype) {
   if (m <= 0 || n <= 0 || k <= 0 || (dtype != 0 && dtype != 1)) return -1;
-  if (m > kStreamMaxM) return kPrefillBase + prefill_pick_tile((int)m, (int)n, (int)k);
+  if (m > kStreamMaxM) {
+    GemmCall g;
+    std::memset(&g, 0, sizeof(g));
+    g.m = static_cast<int>(m);
+    g.n = static_cast<int>(n);
+    g.k = static_cast<int>(k);
+    g.group_size = group_size;
+    g.dtype = dtype;
+    int tile = 0, S = 1;
+    prefill_pick(g, &tile, &S);
+    return prefill_id(tile, S);
+  }
   const int mm = static_cast<int>(m < 32 ? m : 32);
   if (g_stream_v2) {
     GemmCall g;
@@ -364,9 +399,31 @@ int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int 
   return 1 + decode_index(dtype, nt_for_m(mm), group_size != -1, pick_geometry(mm, (int)n, (int)k));
 }
 
+int b200_w4a16_max_clusters(int config, int64_t m, int group_size, int dtype) {
+  GemmCall g;
+  std::memset(&g, 0, sizeof(g));
+  g.m = static_cast<int>(m);
+  g.n = 4096;
+  g.k = 4096;
+  g.group_size = group_size;
+  g.dtype = dtype;
+  if (config >= kStreamBase && config < kStreamBase + kStreamGeoms * 4)
+    return stream_max_clusters(g, (config - kStreamBase) >> 2, 1 << ((config - kStreamBase) & 3));
+  if (config >= kPrefillBase && config < kPrefillBase + kPrefillIds) {
+    int tile, S;
+    prefill_from_id(config, &tile, &S);
+    return prefill_max_clusters(g, tile, S);
+  }
+  return -1;
+}
+
 const char* b200_w4a16_config_name(int config) {
   const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
-  if (config >= kPrefillBase && config < kPrefillBase + kPrefillTiles) return prefill_tile_name(config - kPrefillBase);
+  if (config >= kPrefillBase && config < kPrefillBase + kPrefillIds) {
+    int tile, S;
+    prefill_from_id(config, &tile, &S);
+    return prefill_tile_name(tile);
+  }
   if (config >= kStreamBase && config < kStreamBase + kStreamGeoms * 4) return stream_geom_name((config - kStreamBase) >> 2);
   if (config < 1 || config > count) return "";
   return g_decode[config - 1].name;
@@ -422,7 +479,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
   const int forced = opts ? opts->force_config : 0;
   // ---- tensor-bound regime: one persistent tcgen05 launch for any M ----
   if ((forced == 0 && m > kStreamMaxM) || (forced >= kPrefillBase && forced < kStreamBase)) {
-    if (forced >= kPrefillBase + kPrefillTiles)
+    if (forced >= kPrefillBase + kPrefillIds)
       return fail(B200_W4A16_EINVAL, "force_config %d out of range", forced);
     GemmCall g;
     g.a = a;
@@ -440,7 +497,10 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     g.dtype = dtype;
     g.pdl = opts ? (opts->pdl != 0) : (g_default_pdl.load(std::memory_order_relaxed) != 0);
     g.stream = st;
-    return launch_prefill(g, forced ? forced - kPrefillBase : prefill_pick_tile(g.m, g.n, g.k));
+    int tile, S;
+    if (forced) prefill_from_id(forced, &tile, &S);
+    else prefill_pick(g, &tile, &S);
+    return launch_prefill(g, tile, S);
   }
   // ---- streaming regime: needs the fp32 split-K scratch ----
   {

@@ -1,6 +1,7 @@
 // Host side of the tcgen05 regime: tile-shape choice, TMA descriptors, launch.
 // (the reference's host logic for large M is the `par` M-loop of marlin_mm, gptq_marlin_mm.cu:161-206;
 //  here one persistent launch covers any M.)
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/b200_w4a16.h"
@@ -21,18 +22,49 @@ const TileShape kTiles[kPrefillTiles] = {
     {1, 256, 0.95f, "tc/bn128/bm256"},
     {2, 128, 0.85f, "tc/bn256/bm128"},
     {1, 128, 0.75f, "tc/bn128/bm128"},
+    // split-K over a thread-block cluster (mid M: the N x M grid alone cannot fill the machine)
+    {1, 64, 0.f, "tc/bn128/bm64/splitk"},
+    {1, 128, 0.f, "tc/bn128/bm128/splitk"},
 };
 
-template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED>
-int launch_one(const GemmCall& g) {
-  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED>;
-  auto kern = w4a16_prefill_kernel<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED>;
+template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT>
+int launch_one(const GemmCall& g, int S, int* query) {
+  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
+  auto kern = w4a16_prefill_kernel<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
   static bool attr_set = false;  // benign race: idempotent
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess)
       return fail(B200_W4A16_ECUDA, "cudaFuncSetAttribute(smem=%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
     attr_set = true;
+  }
+  if (query) {
+    // clusters of S such CTAs the device can hold at once (cached per kernel and S)
+    static int cache[4] = {0, 0, 0, 0};
+    int li = 0;
+    while ((1 << li) < S) ++li;
+    if (cache[li] == 0) {
+      cudaLaunchConfig_t qc;
+      std::memset(&qc, 0, sizeof(qc));
+      qc.gridDim = dim3(S * 64);
+      qc.blockDim = dim3(Cfg::THREADS);
+      qc.dynamicSmemBytes = Cfg::SMEM_BYTES;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = S;
+      qa[0].val.clusterDim.y = 1;
+      qa[0].val.clusterDim.z = 1;
+      qc.attrs = qa;
+      qc.numAttrs = 1;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &qc) != cudaSuccess || n < 1) {
+        (void)cudaGetLastError();
+        n = -1;
+      }
+      cache[li] = n;
+    }
+    *query = cache[li];
+    return 0;
   }
   CUtensorMap tm_w, tm_s, tm_a;
   {  // weights: int32 [K/16][N/64][128]; chunks past N/64 are zero-filled
@@ -72,8 +104,15 @@ int launch_one(const GemmCall& g) {
   args.n_tiles = (g.n + Cfg::BN - 1) / Cfg::BN;
   args.m_tiles = (g.m + BM - 1) / BM;
   args.kblks = g.k / 64;
+  static const int dbg = [] { const char* e = std::getenv("B200_W4A16_DBG_TC"); return e ? std::atoi(e) : 0; }();
+  args.dbg = dbg;
   const long long tiles = static_cast<long long>(args.n_tiles) * args.m_tiles;
-  const int grid = static_cast<int>(tiles < sm_count() ? tiles : sm_count());
+  int grid = static_cast<int>(tiles < sm_count() ? tiles : sm_count());
+  if (SPLIT) {
+    if (S > args.kblks) S = args.kblks;
+    while (S & (S - 1)) --S;
+    grid = static_cast<int>(tiles) * S;
+  }
 
   cudaLaunchConfig_t cfg;
   std::memset(&cfg, 0, sizeof(cfg));
@@ -81,11 +120,22 @@ int launch_one(const GemmCall& g) {
   cfg.blockDim = dim3(Cfg::THREADS);
   cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = g.stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (SPLIT && S > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = S;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (g.pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = g.pdl ? 1 : 0;
+  cfg.numAttrs = na;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tm_w, tm_s, tm_a, args);
   if (e != cudaSuccess) return fail(B200_W4A16_ECUDA, "tcgen05 kernel launch: %s", cudaGetErrorString(e));
   g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -93,12 +143,14 @@ int launch_one(const GemmCall& g) {
 }
 
 template <typename T, bool GROUPED>
-int launch_tile(const GemmCall& g, int tile) {
+int launch_tile(const GemmCall& g, int tile, int S, int* query) {
   switch (tile) {
-    case 0: return launch_one<T, 2, 256, 3, 3, 4, GROUPED>(g);
-    case 1: return launch_one<T, 1, 256, 4, 4, 4, GROUPED>(g);
-    case 2: return launch_one<T, 2, 128, 4, 3, 8, GROUPED>(g);
-    case 3: return launch_one<T, 1, 128, 6, 6, 4, GROUPED>(g);
+    case 0: return launch_one<T, 2, 256, 3, 3, 4, GROUPED, false>(g, 1, query);
+    case 1: return launch_one<T, 1, 256, 4, 4, 4, GROUPED, false>(g, 1, query);
+    case 2: return launch_one<T, 2, 128, 4, 3, 8, GROUPED, false>(g, 1, query);
+    case 3: return launch_one<T, 1, 128, 6, 6, 4, GROUPED, false>(g, 1, query);
+    case 4: return launch_one<T, 1, 64, 2, 10, 8, GROUPED, true>(g, S, query);
+    case 5: return launch_one<T, 1, 128, 2, 8, 8, GROUPED, true>(g, S, query);
   }
   return fail(B200_W4A16_EINVAL, "tcgen05 tile id %d out of range", tile);
 }
@@ -109,13 +161,44 @@ const char* prefill_tile_name(int tile) {
   return (tile >= 0 && tile < kPrefillTiles) ? kTiles[tile].name : "";
 }
 
-// widest tile whose wave quantisation on this device does not cost more than its size gains
-int prefill_pick_tile(int m, int n, int k) {
-  (void)k;
+namespace {
+int dispatch(const GemmCall& g, int tile, int S, int* query) {
+  const bool grouped = g.group_size != -1;
+  if (S < 1) S = 1;
+  if (S > 8) S = 8;
+  if (g.dtype == 0)
+    return grouped ? launch_tile<__half, true>(g, tile, S, query) : launch_tile<__half, false>(g, tile, S, query);
+  return grouped ? launch_tile<__nv_bfloat16, true>(g, tile, S, query)
+                 : launch_tile<__nv_bfloat16, false>(g, tile, S, query);
+}
+}  // namespace
+
+// shape -> (tile, cluster size).  Large M: the widest whole-K tile whose wave quantisation on this
+// device does not cost more than its size gains.  Mid M (one or two token tiles): split-K clusters,
+// as wide as still fits the device in ONE wave of clusters.
+void prefill_pick(const GemmCall& g, int* tile_out, int* S_out) {
+  const int m = g.m, n = g.n;
   const int sms = sm_count();
+  if (m <= 256) {
+    // split-K tiles: two CTAs are resident per SM (87-110 KB each); clusters pack GPCs imperfectly, so
+    // budget ~90 % of the 2 x SMs slots (measured on B200: 32 clusters of 8 are co-resident, 36 are
+    // not; cudaOccupancyMaxActiveClusters under-reports this kernel, profiles/r01/README.md)
+    const int t = m <= 64 ? 4 : 5;
+    const int bm = kTiles[t].bm;
+    const int tiles = ((n + 127) / 128) * ((m + bm - 1) / bm);
+    const int kblks = g.k / 64;
+    const int cap = (2 * sms * 9) / 10;
+    int s = 8;
+    while (s > 1 && (kblks / s < 4 || tiles * s > cap)) s >>= 1;
+    if (m <= 128 || tiles <= cap) {
+      *tile_out = t;
+      *S_out = s;
+      return;
+    }
+  }
   int best = 0;
   float best_score = -1.f;
-  for (int t = 0; t < kPrefillTiles; ++t) {
+  for (int t = 0; t < 4; ++t) {
     const int bn = kTiles[t].nsub * 128, bm = kTiles[t].bm;
     const long long nt = (n + bn - 1) / bn, mt = (m + bm - 1) / bm, tiles = nt * mt;
     const long long waves = (tiles + sms - 1) / sms;
@@ -129,14 +212,15 @@ int prefill_pick_tile(int m, int n, int k) {
       best = t;
     }
   }
-  return best;
+  *tile_out = best;
+  *S_out = 1;
 }
 
-int launch_prefill(const GemmCall& g, int tile) {
-  const bool grouped = g.group_size != -1;
-  if (g.dtype == 0)
-    return grouped ? launch_tile<__half, true>(g, tile) : launch_tile<__half, false>(g, tile);
-  return grouped ? launch_tile<__nv_bfloat16, true>(g, tile) : launch_tile<__nv_bfloat16, false>(g, tile);
+int launch_prefill(const GemmCall& g, int tile, int S) { return dispatch(g, tile, S, nullptr); }
+int prefill_max_clusters(const GemmCall& g, int tile, int S) {
+  int n = -1;
+  if (dispatch(g, tile, S, &n) != 0) return -1;
+  return n;
 }
 
 }  // namespace b200

@@ -213,5 +213,6 @@ void stream_pick(const GemmCall& g, int* geom, int* S) {
 }
 
 int launch_stream(const GemmCall& g, int geom, int S) { return dispatch(g, geom, S, nullptr); }
+int stream_max_clusters(const GemmCall& g, int geom, int S) { return max_clusters(g, geom, S); }
 
 }  // namespace b200

@@ -127,6 +127,9 @@ int64_t b200_w4a16_workspace_ints(int64_t n);
 int64_t b200_w4a16_launch_count(void);
 int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int dtype);
 const char* b200_w4a16_config_name(int config);
+/* clusters of the configuration's CTAs the current device holds at once (cudaOccupancyMaxActiveClusters);
+ * -1 when unknown (no device) or the configuration does not use clusters.  Tuning / tests only. */
+int b200_w4a16_max_clusters(int config, int64_t m, int group_size, int dtype);
 const char* b200_w4a16_last_error(void);
 const char* b200_w4a16_version(void);
 

@@ -205,6 +205,30 @@ def test_all_tcgen05_tiles_agree(dtype):
             assert torch.equal(outs[0], o)
 
 
+@pytest.mark.parametrize("m,k,n", [(33, 1024, 448), (64, 2048, 1152), (100, 512, 256), (128, 1024, 640)])
+def test_tcgen05_splitk_clusters(m, k, n):
+    """mid-M regime: tcgen05 tiles with the K range split over a cluster of 1/2/4/8 CTAs and reduced
+    through distributed shared memory in rank order — oracle-correct, bit-identical run to run."""
+    from cpmcu_b200 import capi as L
+    prob = mo.make_problem(m, k, n, 128, mo.FP16, seed=m + k)
+    c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, mo.FP16)
+    seen = 0
+    for cfg in range(1005, 1013):
+        name = L.config_name(cfg)
+        assert "splitk" in name
+        if "bm64" in name and m > 64:
+            continue
+        out1, _ = run_ours(prob, m, n, k, mo.FP16, force_config=cfg)
+        out2, _ = run_ours(prob, m, n, k, mo.FP16, force_config=cfg, pdl=True)
+        assert torch.equal(out1, out2), f"{name} cfg {cfg}: not deterministic"
+        st = mo.error_stats(out1.cpu().numpy(), exact, mo.FP16)
+        assert st["max_rel"] <= TOL_MAX_REL, (name, cfg, st)
+        seen += 1
+    assert seen >= 4
+    # the heuristic's own choice for this shape is one of them
+    assert "tc/" in L.config_name(L.pick_config(m, n, k))
+
+
 def test_act_order_gather():
     """has_act_order + is_k_full: A's columns are gathered by perm, weights are already group-sorted."""
     b = _b()

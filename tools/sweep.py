@@ -49,7 +49,7 @@ def main():
     ap.add_argument("--ms", default="1,4,16")
     ap.add_argument("--shapes", default="qkv,o,gate_up,down")
     ap.add_argument("--geoms", default="all")
-    ap.add_argument("--family", default="both", choices=["v1", "v2", "both"])
+    ap.add_argument("--family", default="both", choices=["v1", "v2", "both", "tc", "all"])
     ap.add_argument("--pdl-only", action="store_true")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))
     args = ap.parse_args()
@@ -65,7 +65,8 @@ def main():
             a = torch.randn((m, k), device=dev).half()
             out = torch.empty((m, n), dtype=torch.float16, device=dev)
             ws = torch.zeros(B.workspace_ints(n), dtype=torch.int32, device=dev)
-            ct = torch.empty(max(B.reduce_bytes(m, n, k) // 4, 64 * n), dtype=torch.float32, device=dev)
+            ct = torch.empty(max(B.reduce_bytes(m, n, k) // 4, ref_marlin.reduce_max_m(m) * n if ref_marlin.available() else 0, 64 * n),
+                             dtype=torch.float32, device=dev)
             # reference Marlin
             ref_out = None
             if ref_marlin.available():
@@ -80,18 +81,28 @@ def main():
             default_cfg = L.pick_config(m, n, k)
             cands = []
             nt = 1 if m <= 8 else (2 if m <= 16 else 4)
-            if args.family in ("v1", "both"):
+            if args.family in ("v1", "both") and m <= 64:
                 for cfg in range(1, 400):
                     cname = L.config_name(cfg)
                     if not cname:
                         break
                     if cname.startswith(f"__half/nt{nt}/") and cname.endswith("true"):
                         cands.append((cfg, cname))
-            if args.family in ("v2", "both"):
+            if args.family in ("v2", "both", "all") and m <= 64:
                 for cfg in range(2001, 2001 + 64):
                     cname = L.config_name(cfg)
                     if cname:
                         cands.append((cfg, f"{cname}/S{1 << ((cfg - 2001) & 3)}"))
+            if args.family in ("tc", "all"):
+                for cfg in range(1001, 1013):
+                    cname = L.config_name(cfg)
+                    if not cname:
+                        continue
+                    if "splitk" in cname:
+                        if ("bm64" in cname and m > 64) or m > 128:
+                            continue
+                        cname = f"{cname}/S{1 << ((cfg - 1005) & 3)}"
+                    cands.append((cfg, cname))
             for cfg, cname in cands:
                 for pdl in ((True,) if args.pdl_only else (False, True)):
                     def run():

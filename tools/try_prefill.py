@@ -65,6 +65,12 @@ def main():
         for (m, k, n) in [(128, 128, 128), (256, 256, 256), (100, 256, 256), (354, 512, 320), (513, 1024, 1152)]:
             worst = max(worst, check(m, k, n, torch.float16, cfg))
         worst = max(worst, check(300, 384, 448, torch.bfloat16, cfg))
+    for cfg in range(1005, 1013):
+        for (m, k, n) in [(16, 256, 128), (40, 1024, 320), (64, 2048, 1152), (100, 512, 256), (128, 4096, 4608)]:
+            if m > 64 and cfg < 1009:
+                continue
+            worst = max(worst, check(m, k, n, torch.float16, cfg))
+        worst = max(worst, check(61, 1024, 448, torch.bfloat16, cfg))
     worst = max(worst, check(1024, 4096, 4608, torch.float16, 0))
     print("worst max_rel:", worst)
     if worst > 1e-2:
