@@ -209,6 +209,10 @@ def main():
     ap.add_argument("--no-pdl", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-detail", action="store_true")
+    ap.add_argument("--workload", default="auto", choices=["auto", "minicpm4", "llama70b"],
+                    help="auto: MiniCPM4-8B linears at N=1, tensor-parallel Llama-3-70B linears at N>1")
+    ap.add_argument("--tp-layers", type=int, default=16)
+    ap.add_argument("--tp-widths", default="1,16,64")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -222,9 +226,9 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: cpmcu_b200 has no CPU path")
 
-    if world > 1:
-        from bench_tp import main_tp  # multi-GPU: tensor-parallel Llama-3-70B shapes (configs[4])
-        return main_tp(args, rank, world, local_rank)
+    if world > 1 or args.workload == "llama70b":
+        from bench_tp import main_tp  # tensor-parallel Llama-3-70B shapes (configs[4])
+        return main_tp(args, rank, world, local_rank, use_reference=(args.impl == "reference"))
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
