@@ -35,7 +35,16 @@ struct DecodeArgs {
   int ncols;      // column tiles = ceil(N / TN)
   int kblks;      // K / KB
   int slot_max;   // slots per column reserved in c_tmp
+  unsigned long long* dbg_ts;  // tuning only: per-CTA phase timestamps or null
 };
+
+__device__ __forceinline__ void dbg_stamp1(const DecodeArgs& p, int slot) {
+  if (p.dbg_ts != nullptr && blockIdx.x < 1024) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.dbg_ts[blockIdx.x * 8 + slot] = t;
+  }
+}
 
 template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED>
 struct DecodeCfg {
@@ -106,6 +115,7 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   __syncthreads();
   // let the next kernel in the stream start its own weight prefetch as early as possible
   pdl_launch_dependents();
+  if (threadIdx.x == 0) dbg_stamp1(p, 0);
 
   const long long units = static_cast<long long>(p.ncols) * p.kblks;
   const int grid = gridDim.x;
@@ -144,6 +154,7 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       const int npre = my_units < STAGES ? my_units : STAGES;
       for (int it = 0; it < npre; ++it) issue_w(it);   // weights do not depend on the prior grid
       pdl_wait_prior_grids();                          // activations do
+      dbg_stamp1(p, 1);
       for (int it = 0; it < npre; ++it) issue_a(it);
       for (int it = npre; it < my_units; ++it) {
         mbar_wait(bar_empty + 8 * (it % STAGES), ((it / STAGES) & 1) ^ 1);
@@ -183,6 +194,7 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   for (int it = 0; it < my_units; ++it) {
     const int s = it % STAGES;
     mbar_wait(bar_full + 8 * s, (it / STAGES) & 1);
+    if (it == 0 && threadIdx.x == 0) dbg_stamp1(p, 2);
 
     uint32_t s_lo[4], s_hi[4];
     if (GROUPED) {
@@ -237,6 +249,7 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
     const bool last_unit = (it == my_units - 1);
     if (b == p.kblks - 1 || last_unit) {
       const int seg_last_b = b;
+      if (threadIdx.x == 0) dbg_stamp1(p, last_unit ? 5 : 3);
       // 1. reduce the WK warps sharing each chunk through shared memory
 #pragma unroll
       for (int r = 0; r < WK; ++r) {
@@ -332,6 +345,7 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
         }
       }
       named_bar_sync(1, NCONS);  // `red` and s_ticket are reusable
+      if (threadIdx.x == 0) dbg_stamp1(p, last_unit ? 7 : 4);
       ++c;
       b = 0;
       seg_first_b = 0;

@@ -43,11 +43,13 @@ int launch_prefill(const GemmCall& g, int tile, int S);
 int prefill_max_clusters(const GemmCall& g, int tile, int S);
 
 // defined in w4a16_stream.cu: the cluster split-K streaming regime (g.m <= 32)
-constexpr int kStreamGeoms = 6;
+constexpr int kStreamGeoms = 10;
 void stream_pick(const GemmCall& g, int* geom, int* S);
 const char* stream_geom_name(int geom);
 int launch_stream(const GemmCall& g, int geom, int S);
 int stream_max_clusters(const GemmCall& g, int geom, int S);
+void stream_debug_timeline(void* buf, long long launches);
+unsigned long long* stream_debug_next_slot();
 
 // Upper bound on the number of CTAs whose unit ranges intersect one column of `kblks` units when
 // `units` units are split evenly over `grid` CTAs (every CTA gets floor or ceil of units/grid):

@@ -235,6 +235,12 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
           const int r = rp + Cfg::WPC * i;
           q[i] = lds128(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE + (r * CHUNKS + ch) * 512 + lane * 16);
         }
+        // the slot may be overwritten by TMA as soon as it is released: make the release wait for the
+        // LDS results (an arrive has no data dependency on outstanding loads by itself)
+#pragma unroll
+        for (int i = 0; i < Cfg::RPW; ++i)
+          asm volatile("" ::"r"(q[i].x), "r"(q[i].y), "r"(q[i].z), "r"(q[i].w) : "memory");
+        asm volatile("" ::"r"(s_lo[0]), "r"(s_lo[1]), "r"(s_lo[2]), "r"(s_lo[3]) : "memory");
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);  // raw slot is in registers now
 

@@ -29,7 +29,16 @@ struct StreamArgs {
   int m, n, k;
   int kblks;             // K / KB
   int dbg_skip;          // tuning only: 1 = consumers release stages without computing (memory-pipeline ceiling)
+  unsigned long long* dbg_ts;  // tuning only: per-CTA phase timestamps (8 x u64 per CTA, first 1024 CTAs) or null
 };
+
+__device__ __forceinline__ void dbg_stamp(const StreamArgs& p, int slot) {
+  if (p.dbg_ts != nullptr && blockIdx.x < 1024) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.dbg_ts[blockIdx.x * 8 + slot] = t;
+  }
+}
 
 template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED>
 struct StreamCfg {
@@ -49,9 +58,12 @@ struct StreamCfg {
   static constexpr int OFF_A = 0;
   static constexpr int OFF_W = OFF_A + STAGES * A_STAGE;
   static constexpr int OFF_S = OFF_W + STAGES * W_STAGE;
-  static constexpr int OFF_RED = (OFF_S + STAGES * S_STAGE + 127) / 128 * 128;
-  static constexpr int OFF_BAR = OFF_RED + RED_BYTES;
-  static constexpr int SMEM_BYTES = OFF_BAR + 2 * STAGES * 8 + 16 + 1024;
+  // the fp32 partial tile ALIASES the rings: it is written only after every consumer warp has
+  // drained its last stage (named barrier), when no TMA write is outstanding any more
+  static constexpr int OFF_RED = 0;
+  static constexpr int RING_BYTES = (OFF_S + STAGES * S_STAGE + 127) / 128 * 128;
+  static constexpr int OFF_BAR = RING_BYTES > RED_BYTES ? RING_BYTES : (RED_BYTES + 127) / 128 * 128;
+  static constexpr int SMEM_BYTES = OFF_BAR + 2 * STAGES * 8 + 16;
   static constexpr int THREADS = WARPS * 32 + 32;
   static_assert(WARPS % CHUNKS == 0 && KROWS % WK == 0, "warp layout");
   static_assert(KB % 64 == 0, "stage k must be a multiple of the 128-byte activation row");
@@ -59,7 +71,7 @@ struct StreamCfg {
 };
 
 template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED>
-__global__ void __launch_bounds__(WARPS * 32 + 32)
+__global__ void __launch_bounds__(WARPS * 32 + 32, (WARPS >= 16 && NT <= 2) ? 2 : 0)
 w4a16_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_s,
                     const __grid_constant__ CUtensorMap tm_a, const StreamArgs p) {
   using Cfg = StreamCfg<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>;
@@ -67,12 +79,13 @@ w4a16_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   constexpr int MT = Cfg::MT, TNP = Cfg::TNP;
   constexpr int NCONS = WARPS * 32;
 
-  extern __shared__ uint8_t smem_raw[];
   // identical carve-up in every CTA of the cluster (same dynamic smem base), so a local offset
-  // maps to the same object in a peer CTA
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // maps to the same object in a peer CTA.  No static shared memory in this kernel: the dynamic
+  // window starts 1024-aligned (needed by the 128B-swizzled activation boxes); checked, not assumed.
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
   const uint32_t sbase = smem_u32(smem);
+  if ((sbase & 1023u) != 0u) __trap();
   float* red = reinterpret_cast<float*>(smem + Cfg::OFF_RED);
   const uint32_t bar_full = sbase + Cfg::OFF_BAR;
   const uint32_t bar_empty = bar_full + STAGES * 8;
@@ -93,6 +106,7 @@ w4a16_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   }
   __syncthreads();
   pdl_launch_dependents();
+  if (threadIdx.x == 0) dbg_stamp(p, 0);
 
   // this CTA's K range, in k-blocks of KB
   const int kb0 = static_cast<int>((static_cast<long long>(rank) * p.kblks) / S);
@@ -128,6 +142,7 @@ w4a16_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       const int npre = my_blks < STAGES ? my_blks : STAGES;
       for (int it = 0; it < npre; ++it) issue_w(it);  // weights do not depend on the prior grid
       pdl_wait_prior_grids();                         // activations do
+      dbg_stamp(p, 1);
       for (int it = 0; it < npre; ++it) issue_a(it);
       for (int it = npre; it < my_blks; ++it) {
         mbar_wait(bar_empty + 8 * (it % STAGES), ((it / STAGES) & 1) ^ 1);
@@ -155,6 +170,7 @@ w4a16_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
     for (int it = 0; it < my_blks; ++it) {
       const int s = it % STAGES;
       mbar_wait(bar_full + 8 * s, (it / STAGES) & 1);
+      if (it == 0 && threadIdx.x == 0) dbg_stamp(p, 2);
 
       if (p.dbg_skip) {
         __syncwarp();
@@ -211,6 +227,8 @@ w4a16_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
     }
 
     // ---- reduce the WK warps sharing each chunk through shared memory (fixed order) ----
+    if (threadIdx.x == 0) dbg_stamp(p, 3);
+    named_bar_sync(1, NCONS);  // the partial tile aliases the rings: every warp is past its last stage
 #pragma unroll
     for (int r = 0; r < WK; ++r) {
       if (wk == r) {
@@ -231,8 +249,10 @@ w4a16_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   }
 
   // ---- cluster reduction: publish, then CTA `rank` finishes slice `rank` of the tile ----
+  if (threadIdx.x == 0) dbg_stamp(p, 4);
   if (S > 1) cluster_sync_all(); else __syncthreads();
   pdl_wait_prior_grids();  // every thread: C / residual are shared with prior grids
+  if (threadIdx.x == 0) dbg_stamp(p, 5);
 
   if (warp < WARPS) {
     const int col0 = c * TN;
@@ -285,8 +305,10 @@ w4a16_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.c) + goff) = pk;
     }
   }
+  if (threadIdx.x == 0) dbg_stamp(p, 6);
   // no CTA may exit while a peer can still read its shared memory
   if (S > 1) cluster_sync_all();
+  if (threadIdx.x == 0) dbg_stamp(p, 7);
 }
 
 }  // namespace b200

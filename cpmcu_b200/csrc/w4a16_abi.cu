@@ -223,6 +223,7 @@ int launch_decode(const GemmCall& g) {
   const long long slots = static_cast<long long>(sm_count()) * occ;
   const int grid = static_cast<int>(units < slots ? units : slots);
   args.slot_max = decode_slot_max(args.kblks, units, grid);
+  args.dbg_ts = stream_debug_next_slot();
 
   cudaLaunchConfig_t cfg;
   std::memset(&cfg, 0, sizeof(cfg));
@@ -285,7 +286,7 @@ int pick_geometry(int m, int n, int k) {
 
 // configuration ids: 1..count = streaming-kernel configurations, kPrefillBase.. = tcgen05 tile shapes
 constexpr int kPrefillBase = 1001;
-// cluster split-K streaming kernel: id = kStreamBase + geometry * 4 + log2(cluster size)
+// cluster split-K streaming kernel: id = kStreamBase + geometry * 8 + (cluster size - 1)
 constexpr int kStreamBase = 2001;
 // largest M served by the streaming kernel; above it the tcgen05 kernel runs (split-K clusters up to
 // M = 256, persistent whole-K tiles beyond).  Measured crossover on B200: profiles/r01 sweep_mid.
@@ -329,6 +330,7 @@ extern "C" {
 const char* b200_w4a16_last_error(void) { return g_last_error.c_str(); }
 const char* b200_w4a16_version(void) { return "b200-w4a16 0.1 (sm_100a)"; }
 int64_t b200_w4a16_launch_count(void) { return g_launches.load(); }
+void b200_w4a16_debug_timeline(void* device_buf, int64_t launches) { stream_debug_timeline(device_buf, launches); }
 int b200_w4a16_set_pdl(int enable) { return g_default_pdl.exchange(enable ? 1 : 0); }
 
 int b200_w4a16_reduce_max_m(int64_t m) {
@@ -391,10 +393,9 @@ int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int 
     g.k = static_cast<int>(k);
     g.group_size = group_size;
     g.dtype = dtype;
-    int geom = 0, S = 1, l2 = 0;
+    int geom = 0, S = 1;
     stream_pick(g, &geom, &S);
-    while ((1 << l2) < S) ++l2;
-    return kStreamBase + geom * 4 + l2;
+    return kStreamBase + geom * 8 + (S - 1);
   }
   return 1 + decode_index(dtype, nt_for_m(mm), group_size != -1, pick_geometry(mm, (int)n, (int)k));
 }
@@ -407,8 +408,8 @@ int b200_w4a16_max_clusters(int config, int64_t m, int group_size, int dtype) {
   g.k = 4096;
   g.group_size = group_size;
   g.dtype = dtype;
-  if (config >= kStreamBase && config < kStreamBase + kStreamGeoms * 4)
-    return stream_max_clusters(g, (config - kStreamBase) >> 2, 1 << ((config - kStreamBase) & 3));
+  if (config >= kStreamBase && config < kStreamBase + kStreamGeoms * 8)
+    return stream_max_clusters(g, (config - kStreamBase) >> 3, 1 + ((config - kStreamBase) & 7));
   if (config >= kPrefillBase && config < kPrefillBase + kPrefillIds) {
     int tile, S;
     prefill_from_id(config, &tile, &S);
@@ -424,7 +425,7 @@ const char* b200_w4a16_config_name(int config) {
     prefill_from_id(config, &tile, &S);
     return prefill_tile_name(tile);
   }
-  if (config >= kStreamBase && config < kStreamBase + kStreamGeoms * 4) return stream_geom_name((config - kStreamBase) >> 2);
+  if (config >= kStreamBase && config < kStreamBase + kStreamGeoms * 8) return stream_geom_name((config - kStreamBase) >> 3);
   if (config < 1 || config > count) return "";
   return g_decode[config - 1].name;
 }
@@ -547,8 +548,8 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     if (idx < 0) {
       int geom, S;
       if (forced >= kStreamBase) {
-        geom = (forced - kStreamBase) >> 2;
-        S = 1 << ((forced - kStreamBase) & 3);
+        geom = (forced - kStreamBase) >> 3;
+        S = 1 + ((forced - kStreamBase) & 7);
         if (geom >= kStreamGeoms) return fail(B200_W4A16_EINVAL, "force_config %d out of range", forced);
       } else {
         stream_pick(g, &geom, &S);

@@ -9,6 +9,10 @@
 
 namespace b200 {
 
+unsigned long long* g_dbg_ts = nullptr;
+long long g_dbg_ts_launches = 0;
+std::atomic<long long> g_dbg_ts_next{0};
+
 namespace {
 
 struct Geom {
@@ -16,8 +20,10 @@ struct Geom {
   const char* name;
 };
 const Geom kGeoms[kStreamGeoms] = {
-    {2, 8, 8, 6, "st/tn128/kb128/w8"}, {1, 8, 8, 8, "st/tn64/kb128/w8"},  {4, 8, 8, 4, "st/tn256/kb128/w8"},
-    {2, 8, 4, 6, "st/tn128/kb128/w4"}, {4, 4, 8, 6, "st/tn256/kb64/w8"},  {2, 4, 8, 8, "st/tn128/kb64/w8"},
+    {2, 8, 8, 6, "st/tn128/kb128/w8"},   {1, 8, 8, 8, "st/tn64/kb128/w8"},   {4, 8, 8, 4, "st/tn256/kb128/w8"},
+    {2, 8, 4, 6, "st/tn128/kb128/w4"},   {4, 4, 8, 6, "st/tn256/kb64/w8"},   {2, 4, 8, 8, "st/tn128/kb64/w8"},
+    {4, 8, 16, 5, "st/tn256/kb128/w16"}, {2, 8, 16, 6, "st/tn128/kb128/w16"}, {4, 8, 8, 3, "st/tn256/kb128/w8/s3"},
+    {1, 8, 4, 8, "st/tn64/kb128/w4"},
 };
 
 template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED>
@@ -33,9 +39,8 @@ int launch_one(const GemmCall& g, int S, int* query) {
   }
   if (query) {
     // how many clusters of S such CTAs the device can hold at once (cached per kernel and S)
-    static int cache[4] = {0, 0, 0, 0};
-    int li = 0;
-    while ((1 << li) < S) ++li;
+    static int cache[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const int li = S;
     if (cache[li] == 0) {
       cudaLaunchConfig_t qc;
       std::memset(&qc, 0, sizeof(qc));
@@ -99,8 +104,8 @@ int launch_one(const GemmCall& g, int S, int* query) {
   args.kblks = g.k / Cfg::KB;
   static const int dbg_skip = [] { const char* e = std::getenv("B200_W4A16_DBG_SKIP"); return (e && e[0] == '1') ? 1 : 0; }();
   args.dbg_skip = dbg_skip;
+  args.dbg_ts = stream_debug_next_slot();
   if (S > args.kblks) S = args.kblks;
-  while (S & (S - 1)) --S;  // power of two
   const int ncols = (g.n + Cfg::TN - 1) / Cfg::TN;
 
   cudaLaunchConfig_t cfg;
@@ -142,6 +147,10 @@ int launch_geom(const GemmCall& g, int geom, int S, int* query) {
     case 3: return launch_one<T, NT, 2, 8, 4, 6, GROUPED>(g, S, query);
     case 4: return launch_one<T, NT, 4, 4, 8, 6, GROUPED>(g, S, query);
     case 5: return launch_one<T, NT, 2, 4, 8, 8, GROUPED>(g, S, query);
+    case 6: return launch_one<T, NT, 4, 8, 16, 5, GROUPED>(g, S, query);
+    case 7: return launch_one<T, NT, 2, 8, 16, 6, GROUPED>(g, S, query);
+    case 8: return launch_one<T, NT, 4, 8, 8, 3, GROUPED>(g, S, query);
+    case 9: return launch_one<T, NT, 1, 8, 4, 8, GROUPED>(g, S, query);
   }
   return fail(B200_W4A16_EINVAL, "streaming geometry %d out of range", geom);
 }
@@ -210,6 +219,19 @@ void stream_pick(const GemmCall& g, int* geom, int* S) {
   }
   *geom = gm;
   *S = s;
+}
+
+// debug timeline: one 1024-CTA record block per launch, in launch order (null when switched off)
+unsigned long long* stream_debug_next_slot() {
+  if (!g_dbg_ts) return nullptr;
+  const long long idx = g_dbg_ts_next.fetch_add(1, std::memory_order_relaxed);
+  return idx < g_dbg_ts_launches ? g_dbg_ts + idx * 8192 : nullptr;
+}
+
+void stream_debug_timeline(void* buf, long long launches) {
+  g_dbg_ts = static_cast<unsigned long long*>(buf);
+  g_dbg_ts_launches = buf ? launches : 0;
+  g_dbg_ts_next.store(0);
 }
 
 int launch_stream(const GemmCall& g, int geom, int S) { return dispatch(g, geom, S, nullptr); }

@@ -132,6 +132,10 @@ const char* b200_w4a16_config_name(int config);
 int b200_w4a16_max_clusters(int config, int64_t m, int group_size, int dtype);
 const char* b200_w4a16_last_error(void);
 const char* b200_w4a16_version(void);
+/* Tuning aid: when device_buf != NULL the next `launches` streaming-kernel launches record per-CTA
+ * phase timestamps (%globaltimer; 8 x uint64 per CTA, 1024 CTAs = 64 KiB per launch, launch order)
+ * into device_buf (launches * 65536 bytes).  NULL switches it off.  Never used by the product path. */
+void b200_w4a16_debug_timeline(void* device_buf, int64_t launches);
 
 #ifdef __cplusplus
 }

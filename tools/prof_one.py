@@ -17,8 +17,13 @@ ap.add_argument("--m", type=int, default=1)
 ap.add_argument("--cfg", type=int, default=0)
 ap.add_argument("--copies", type=int, default=6)
 ap.add_argument("--pdl", action="store_true")
+ap.add_argument("--cfg-name", default="", help="pick the configuration id by (sub)name, e.g. __half/nt1/tn4x64/kb8x16/w8")
 a_ = ap.parse_args()
 dev = "cuda"
+if a_.cfg_name:
+    from cpmcu_b200 import capi as _L
+    a_.cfg = next(c for c in list(range(1, 400)) + list(range(2001, 2100)) if a_.cfg_name in (_L.config_name(c) or ""))
+    print("cfg", a_.cfg, _L.config_name(a_.cfg))
 k, n, m = a_.k, a_.n, a_.m
 qw = torch.randint(-2**31, 2**31 - 1, (a_.copies, k // 16, 2 * n), dtype=torch.int32, device=dev)
 sc = (torch.rand((a_.copies, k // 128, n), device=dev) * 0.018 + 0.002).half()

@@ -52,7 +52,9 @@ def main():
     ap.add_argument("--family", default="both", choices=["v1", "v2", "both", "tc", "all"])
     ap.add_argument("--pdl-only", action="store_true")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep.json"))
+    ap.add_argument("--ss", default="", help="cluster sizes to try, e.g. 1,2,3,4,6,8 (default all)")
     args = ap.parse_args()
+    args.ss = [int(x) for x in args.ss.split(",")] if args.ss else []
     dev = "cuda"
     results = []
     for name in args.shapes.split(","):
@@ -89,10 +91,11 @@ def main():
                     if cname.startswith(f"__half/nt{nt}/") and cname.endswith("true"):
                         cands.append((cfg, cname))
             if args.family in ("v2", "both", "all") and m <= 64:
-                for cfg in range(2001, 2001 + 64):
+                for cfg in range(2001, 2001 + 128):
                     cname = L.config_name(cfg)
-                    if cname:
-                        cands.append((cfg, f"{cname}/S{1 << ((cfg - 2001) & 3)}"))
+                    S = 1 + ((cfg - 2001) & 7)
+                    if cname and (not args.ss or S in args.ss) and (args.geoms == "all" or str((cfg - 2001) >> 3) in args.geoms.split(",")):
+                        cands.append((cfg, f"{cname}/S{S}"))
             if args.family in ("tc", "all"):
                 for cfg in range(1001, 1013):
                     cname = L.config_name(cfg)

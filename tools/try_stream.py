@@ -22,7 +22,7 @@ for (m, k, n) in [(1, 512, 256), (5, 1024, 320), (16, 2048, 1088), (27, 4096, 46
         ct = torch.empty(max(B.reduce_bytes(m, n, k) // 4, 1), dtype=torch.float32, device=DEV)
         ref = a.double() @ B.dequant(qw, sc, k, n).double()
         first = None
-        for cfg in range(2001, 2001 + 24):
+        for cfg in range(2001, 2001 + 80):
             out = B.gemm(a, qw, sc, ws, ct, force_config=cfg)
             out2 = B.gemm(a, qw, sc, ws, ct, force_config=cfg, pdl=True)
             torch.cuda.synchronize()
@@ -32,7 +32,7 @@ for (m, k, n) in [(1, 512, 256), (5, 1024, 320), (16, 2048, 1088), (27, 4096, 46
             worst = max(worst, rel)
             tol = 1e-2 if dtype == torch.float16 else 2e-2
             flag = "" if rel <= tol else "  <-- FAIL"
-            print(f"m={m:3d} k={k:5d} n={n:5d} {str(dtype)[6:]:8s} cfg={cfg} {capi.config_name(cfg)}/S{1 << ((cfg - 2001) & 3)} "
+            print(f"m={m:3d} k={k:5d} n={n:5d} {str(dtype)[6:]:8s} cfg={cfg} {capi.config_name(cfg)}/S{1 + ((cfg - 2001) & 7)} "
                   f"max_rel={rel:.2e}{flag}", flush=True)
 print("worst", worst)
 print("OK" if worst <= 2e-2 else "FAIL")
