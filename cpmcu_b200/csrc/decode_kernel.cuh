@@ -1,24 +1,29 @@
-// HBM-bound regime (decode / speculative tree-verify, M <= 32): a persistent, warp-specialised
-// weight-streaming kernel.
+// HBM-bound regime (decode / speculative tree-verify, M <= 32 per launch): a PERSISTENT, warp-specialised
+// weight-streaming kernel with stream-K work distribution.
 //
-//   * one CTA per SM; ONE producer lane feeds a STAGES-deep ring of shared-memory stages with TMA
-//     (cp.async.bulk.tensor): a [KB x TN] box of the Marlin int32 stream (evict-first: streamed
-//     once), the matching [M x KB] activation box (128B-swizzled, zero-filled past M) and the
-//     group-scale row.  full/empty mbarriers; the ring keeps >= 64 KB of HBM requests in flight per SM.
-//   * WARPS consumer warps.  Each owns one 64-column chunk and 1/WK of the stage's k-rows; a lane's
-//     16 bytes of a 512-byte Marlin block are the A-operand fragments of four m16n8k16 MMAs once
-//     dequantised (weights are the 16-row M side, tokens the 8-column N side), so the int4 stream
-//     goes LDS.128 -> registers -> lop3/HSUB2/HFMA2 (exact) -> HMUL2 by the group scale (the
-//     reference's single rounding) -> mma.sync with fp32 accumulators.  Nothing is re-staged.
-//   * work = (column tile c, k-block b) units in column-major order, split evenly over the CTAs
-//     (|units_i - units_j| <= 1).  A CTA accumulates a run of k-blocks of one column in registers,
-//     then flushes: warps sharing a column reduce through shared memory; a column whose K range is
-//     split over several CTAs is reduced through fp32 slots in c_tmp in FIXED slot order by
-//     whichever CTA arrives last (atomic ticket in `workspace`, reset to 0) — deterministic, no
-//     spinning, no co-residency assumption (the reference serialises CTAs with a spin lock,
-//     marlin_device_ops.cuh:347-377).
-//   * PDL: the producer prefetches weights/scales for its first STAGES units BEFORE
-//     griddepcontrol.wait, so back-to-back linears keep HBM busy across kernel boundaries.
+//   * grid = one CTA per SM.  Work = (column tile c, k-block b) units in column-major order, split
+//     evenly over the CTAs (|units_i - units_j| <= 1): every SM streams the same number of bytes, for
+//     any shape — no wave quantisation, no cluster placement lottery.
+//   * roles: 1 TMA producer lane, WARPS consumer warps, 1 flusher warp.
+//       producer  feeds a STAGES-deep ring with cp.async.bulk.tensor: a [KROWS x CHUNKS] box of the
+//                 Marlin int32 stream (evict-first), the group's scale row, the [M x KB] activation box
+//                 (128B-swizzled, zero-filled past M).  Weights/scales of the first STAGES units are
+//                 requested BEFORE griddepcontrol.wait (PDL): they do not depend on the prior grid.
+//       consumers LDS.128 -> lop3/HADD2/HFMA2 (exact q-8) -> HMUL2 by the group scale (the reference's
+//                 single rounding) -> mma.sync m16n8k16, weights as the 16-row operand, fp32 accumulate.
+//                 At the end of a column segment the WK warps sharing a chunk reduce into one fp32 tile
+//                 in shared memory (fixed order), hand it to the flusher through an mbarrier and go
+//                 straight on to the next unit.
+//       flusher   turns finished tiles into output OFF the consumers' critical path.  A column whose K
+//                 range is split over several CTAs is reduced through fp32 slots in c_tmp: the CTAs
+//                 holding later K ranges publish their partial and raise a flag in `workspace`
+//                 (st.release); the CTA holding the column's FIRST k-blocks — always the last segment
+//                 of its own range, so it finishes last — acquires the flags, adds the partials in slot
+//                 order (bit-deterministic), writes T, and resets the flags to zero (the reference's
+//                 workspace contract; the reference serialises the CTAs of a column through a spin
+//                 lock instead, marlin_device_ops.cuh:347-377).
+//   * shared memory <= ~110 KB and <= 56 registers for M <= 8, so that with PDL the NEXT linear's CTA is
+//     co-resident on every SM and has its ring full when this kernel drains.
 #pragma once
 #include "common.cuh"
 
@@ -57,19 +62,24 @@ struct DecodeCfg {
   static constexpr int A_SUB = MT * 128;       // bytes of one activation sub-tile
   static constexpr int A_STAGE = KC * A_SUB;
   static constexpr int W_STAGE = KROWS * CHUNKS * 512;
-  static constexpr int S_STAGE = GROUPED ? TN * 2 : 0;
+  static constexpr int SG = KB > 128 ? KB / 128 : 1;  // scale groups (rows of the scale box) per stage
+  static constexpr int S_STAGE = GROUPED ? SG * TN * 2 : 0;
   static constexpr int STAGE_TX = A_STAGE + W_STAGE + S_STAGE;
   static constexpr int TNP = TN + 4;           // padded fp32 row of the reduction tile
   static constexpr int RED_BYTES = MT * TNP * 4;
+  // ring depth: STAGES for M <= 8; one / two fewer for the wider token tiles, whose activation boxes and
+  // reduction tile are bigger, so that the CTA stays under half an SM's shared memory (PDL co-residency)
+  static constexpr int NSTAGE = (NT == 1) ? STAGES : ((NT == 2 ? STAGES - 1 : STAGES - 2) < 2 ? 2 : (NT == 2 ? STAGES - 1 : STAGES - 2));
   static constexpr int OFF_A = 0;
-  static constexpr int OFF_W = OFF_A + STAGES * A_STAGE;
-  static constexpr int OFF_S = OFF_W + STAGES * W_STAGE;
-  static constexpr int OFF_RED = (OFF_S + STAGES * S_STAGE + 127) / 128 * 128;
+  static constexpr int OFF_W = OFF_A + NSTAGE * A_STAGE;
+  static constexpr int OFF_S = OFF_W + NSTAGE * W_STAGE;
+  static constexpr int OFF_RED = (OFF_S + NSTAGE * S_STAGE + 127) / 128 * 128;
   static constexpr int OFF_BAR = OFF_RED + RED_BYTES;
-  static constexpr int SMEM_BYTES = OFF_BAR + 2 * STAGES * 8 + 16 + 1024;  // +1024: manual alignment
-  static constexpr int THREADS = WARPS * 32 + 32;
+  static constexpr int SMEM_BYTES = OFF_BAR + (2 * NSTAGE + 2) * 8 + 16;
+  static constexpr int THREADS = WARPS * 32 + 64;  // + producer warp + flusher warp
+  static constexpr int FLAGS_PER_TILE = CHUNKS * 16;  // ints of `workspace` owned by one column tile
   static_assert(WARPS % CHUNKS == 0 && KROWS % WK == 0, "warp layout");
-  static_assert(KB % 64 == 0, "stage k must be a multiple of the 128-byte activation row");
+  static_assert(KB % 64 == 0 && (KB <= 128 || (KB == 256 && WK <= 8)), "stage k: a multiple of the 128-byte activation row; one group, or two whole groups");
   static_assert(A_SUB % 1024 == 0 && W_STAGE % 1024 == 0, "TMA swizzle alignment");
 };
 
@@ -82,34 +92,99 @@ __device__ __forceinline__ int cta_of_unit(long long u, long long units, int gri
   return static_cast<int>(((u + 1) * grid - 1) / units);
 }
 
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// converts 4 fp32 sums to T with the reference's rounding points (RN to T; channelwise scale on the
+// ROUNDED sum, marlin_kernel_impl.cuh:957-963; then residual, then bias) and stores them
+template <typename T, bool GROUPED>
+__device__ __forceinline__ void emit_out(const DecodeArgs& p, int tok, int n, float4 v) {
+  T o[4] = {Elem<T>::from_float(v.x), Elem<T>::from_float(v.y), Elem<T>::from_float(v.z),
+            Elem<T>::from_float(v.w)};
+  if (!GROUPED) {
+    const T* sc = reinterpret_cast<const T*>(p.scales);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o[e] = __hmul(o[e], sc[chan_scale_pos(n + e)]);
+  }
+  const size_t off = static_cast<size_t>(tok) * p.n + n;
+  if (p.residual) {
+    const T* rs = reinterpret_cast<const T*>(p.residual) + off;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o[e] = __hadd(rs[e], o[e]);
+  }
+  if (p.bias) {
+    const T* bs = reinterpret_cast<const T*>(p.bias) + n;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o[e] = __hadd(o[e], bs[e]);
+  }
+  uint2 pk;
+  pk.x = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[0])) |
+         (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[1])) << 16);
+  pk.y = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[2])) |
+         (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[3])) << 16);
+  *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.c) + off) = pk;
+}
+
+// the sharers of column tile c under the even unit split: CTAs cta_first..cta_last, slot = cta - cta_first
+struct ColumnShare {
+  int nparts, my_slot;
+  float* slots;   // c_tmp slots of this column: [slot][m][TN] fp32
+  int* flags;     // one int per slot in `workspace` (slot 0, the owner's, stays unused)
+  size_t slot_elems;
+};
+template <int TN, int FLAGS_PER_TILE>
+__device__ __forceinline__ ColumnShare column_share(const DecodeArgs& p, int c, long long units, int grid) {
+  const long long ufirst = static_cast<long long>(c) * p.kblks;
+  const int cta_first = cta_of_unit(ufirst, units, grid);
+  const int cta_last = cta_of_unit(ufirst + p.kblks - 1, units, grid);
+  ColumnShare cs;
+  cs.nparts = cta_last - cta_first + 1;
+  cs.my_slot = static_cast<int>(blockIdx.x) - cta_first;
+  cs.slot_elems = static_cast<size_t>(p.m) * TN;
+  cs.slots = p.c_tmp + static_cast<size_t>(c) * p.slot_max * cs.slot_elems;
+  cs.flags = p.workspace + c * FLAGS_PER_TILE;
+  return cs;
+}
+
 template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED>
-__global__ void __launch_bounds__(WARPS * 32 + 32, (NT <= 2 && WARPS == 8) ? 2 : 1)
+__global__ void __launch_bounds__(WARPS * 32 + 64, (NT == 1 || (NT == 2 && WARPS <= 8)) ? 2 : 1)
 w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_s,
                     const __grid_constant__ CUtensorMap tm_a, const DecodeArgs p) {
   using Cfg = DecodeCfg<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>;
-  using T2 = typename Elem<T>::T2;
   constexpr int TN = Cfg::TN, KB = Cfg::KB, WK = Cfg::WK, RPW = Cfg::RPW, KC = Cfg::KC;
-  constexpr int MT = Cfg::MT, TNP = Cfg::TNP;
+  constexpr int TNP = Cfg::TNP;
+  constexpr int NS = Cfg::NSTAGE;  // ring depth
   constexpr int NCONS = WARPS * 32;
 
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // no static shared memory in this kernel: the dynamic window starts 1024-aligned (needed by the
+  // 128B-swizzled activation boxes); checked, not assumed
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
   const uint32_t sbase = smem_u32(smem);
+  if ((sbase & 1023u) != 0u) __trap();
   float* red = reinterpret_cast<float*>(smem + Cfg::OFF_RED);
   const uint32_t bar_full = sbase + Cfg::OFF_BAR;
-  const uint32_t bar_empty = bar_full + STAGES * 8;
-  volatile int* s_ticket = reinterpret_cast<volatile int*>(smem + Cfg::OFF_BAR + 2 * STAGES * 8);
+  const uint32_t bar_empty = bar_full + NS * 8;
+  const uint32_t bar_red_full = bar_empty + NS * 8;   // consumers -> flusher: tile complete
+  const uint32_t bar_red_empty = bar_red_full + 8;        // flusher -> consumers: tile consumed
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
 #pragma unroll
-    for (int s = 0; s < STAGES; ++s) {
+    for (int s = 0; s < NS; ++s) {
       mbar_init(bar_full + 8 * s, 1);
       mbar_init(bar_empty + 8 * s, WARPS);
     }
+    mbar_init(bar_red_full, WARPS);
+    mbar_init(bar_red_empty, 1);
     fence_barrier_init();
   }
   __syncthreads();
@@ -122,6 +197,7 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   const int u0 = unit_begin(blockIdx.x, units, grid);
   const int u1 = unit_begin(blockIdx.x + 1, units, grid);
   const int my_units = u1 - u0;
+  if (my_units == 0) return;
 
   if (warp == WARPS) {
     // ===================================== producer =====================================
@@ -129,10 +205,8 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       tma_prefetch_desc(&tm_w);
       tma_prefetch_desc(&tm_a);
       if (GROUPED) tma_prefetch_desc(&tm_s);
-      auto issue_w = [&](int it) {
-        const int u = u0 + it;
-        const int c = u / p.kblks, b = u - c * p.kblks;
-        const int s = it % STAGES;
+      const int c0 = u0 / p.kblks, b0 = u0 - c0 * p.kblks;
+      auto issue_w = [&](int s, int c, int b) {
         const uint32_t full = bar_full + 8 * s;
         mbar_arrive_expect_tx(full, Cfg::STAGE_TX);
         tma_load_3d(sbase + Cfg::OFF_W + s * Cfg::W_STAGE, &tm_w, full, 0, c * CHUNKS, b * KROWS,
@@ -141,34 +215,84 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
           tma_load_3d(sbase + Cfg::OFF_S + s * Cfg::S_STAGE, &tm_s, full, 0, c * CHUNKS,
                       (b * KB) / 128, kEvictLast);
       };
-      auto issue_a = [&](int it) {
-        const int u = u0 + it;
-        const int b = u % p.kblks;
-        const int s = it % STAGES;
+      auto issue_a = [&](int s, int b) {
         const uint32_t full = bar_full + 8 * s;
 #pragma unroll
         for (int kc = 0; kc < KC; ++kc)
           tma_load_2d(sbase + Cfg::OFF_A + s * Cfg::A_STAGE + kc * Cfg::A_SUB, &tm_a, full,
                       b * KB + kc * 64, 0, kEvictLast);
       };
-      const int npre = my_units < STAGES ? my_units : STAGES;
-      for (int it = 0; it < npre; ++it) issue_w(it);   // weights do not depend on the prior grid
-      pdl_wait_prior_grids();                          // activations do
+      const int npre = my_units < NS ? my_units : NS;
+      int c = c0, b = b0;
+      for (int it = 0; it < npre; ++it) {   // weights do not depend on the prior grid
+        issue_w(it, c, b);
+        if (++b == p.kblks) { b = 0; ++c; }
+      }
+      pdl_wait_prior_grids();               // activations do
       dbg_stamp1(p, 1);
-      for (int it = 0; it < npre; ++it) issue_a(it);
+      {
+        int bb = b0;
+        for (int it = 0; it < npre; ++it) {
+          issue_a(it, bb);
+          if (++bb == p.kblks) bb = 0;
+        }
+      }
+      int s = npre % NS;
+      uint32_t ph = (npre == NS) ? 0u : 1u;  // parity of the empty-barrier phase to wait for
       for (int it = npre; it < my_units; ++it) {
-        mbar_wait(bar_empty + 8 * (it % STAGES), ((it / STAGES) & 1) ^ 1);
-        issue_w(it);
-        issue_a(it);
+        mbar_wait(bar_empty + 8 * s, ph);
+        issue_w(s, c, b);
+        issue_a(s, b);
+        if (++b == p.kblks) { b = 0; ++c; }
+        if (++s == NS) { s = 0; ph ^= 1u; }
       }
     }
     return;
   }
 
-  // ======================================= consumers =======================================
-  pdl_wait_prior_grids();  // before any global write (C, c_tmp, workspace are shared with prior grids)
-  if (my_units == 0) return;
+  if (warp == WARPS + 1) {
+    // ======================================= flusher =======================================
+    // walks the same column segments as the consumers; every global write of the kernel is here
+    pdl_wait_prior_grids();  // C, c_tmp and the flags are shared with prior grids
+    int u = u0;
+    uint32_t seg = 0;
+    while (true) {
+      const int c = u / p.kblks;
+      const int b_first = u - c * p.kblks;
+      const int col_end = (c + 1) * p.kblks;
+      const int uend = u1 < col_end ? u1 : col_end;
+      if (uend == u1) break;  // the CTA's last segment is finished by the consumer warps themselves
+      const bool whole = (b_first == 0);
+      mbar_wait_backoff(bar_red_full, seg & 1u, 64);
+      const int items = p.m * (TN / 4);  // float4 items of the valid token rows
+      const int col0 = c * TN;
+      if (whole) {
+        for (int e = lane; e < items; e += 32) {
+          const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
+          if (col0 + nn < p.n)
+            emit_out<T, GROUPED>(p, tok, col0 + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn));
+        }
+      } else {
+        // an early segment that does not start its column: publish the fp32 partial, raise the flag
+        const ColumnShare cs = column_share<TN, Cfg::FLAGS_PER_TILE>(p, c, units, grid);
+        float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
+        for (int e = lane; e < items; e += 32) {
+          const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
+          __stcg(reinterpret_cast<float4*>(mine + static_cast<size_t>(e) * 4),
+                 *reinterpret_cast<const float4*>(red + tok * TNP + nn));
+        }
+        __syncwarp();  // the release below is cumulative over the stores ordered before it by this barrier
+        if (lane == 0) st_release_gpu(cs.flags + cs.my_slot, 1);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_red_empty);
+      u = uend;
+      ++seg;
+    }
+    return;
+  }
 
+  // ======================================= consumers =======================================
   const int wn = warp % CHUNKS;  // chunk (64 columns) of the tile
   const int wk = warp / CHUNKS;  // k-row phase
   const int g = lane >> 2, t = lane & 3;
@@ -181,76 +305,80 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
 #pragma unroll
       for (int e = 0; e < 4; ++e) acc[j][nt][e] = 0.f;
 
-  // ldmatrix source row/chunk of this lane inside a 128B-swizzled [MT][64] activation sub-tile
-  //   NT==1 (.x2): lanes 0-7 -> k 0..7 of the k16 step, lanes 8-15 -> k 8..15 (16-31 ignored)
-  //   NT>=2 (.x4): lanes 16-31 -> token rows 8..15 of the pair
+  // per-lane byte offsets inside a stage, fixed for the whole kernel (three registers):
+  //   weights: k16-row r = wk + WK*i, chunk wn -> block (r*CHUNKS + wn) = warp + i*WARPS, so this lane's
+  //     16 B sit at threadIdx.x*16 + i*(WARPS*512)
+  //   activations (ldmatrix row address inside the 128B-swizzled [MT][64] sub-tile of row r):
+  //     NT==1 (.x2): lanes 0-7 -> k 0..7 of the k16 step, lanes 8-15 -> k 8..15 (16-31 ignored)
+  //     NT>=2 (.x4): lanes 16-31 -> token rows 8..15 of the pair
+  //     r = wk | (WK*i) (disjoint bits), so the address is a lane constant XOR / plus compile-time terms
   const int lm_row = (lane & 7) + ((NT >= 2 && (lane & 16)) ? 8 : 0);
   const int lm_half = (lane >> 3) & 1;
+  const uint32_t q_lane = threadIdx.x * 16u;
+  const uint32_t a_lane = static_cast<uint32_t>((wk >> 2) * Cfg::A_SUB + lm_row * 128 +
+                                                ((((wk & 3) << 1) ^ lm_half ^ (lm_row & 7)) << 4));
+  const uint32_t s_off = static_cast<uint32_t>(wn * 128 + g * 16);
 
-  int c = u0 / p.kblks;
-  int b = u0 - c * p.kblks;
-  int seg_first_b = b;
+  int b = u0 % p.kblks;   // k-block of the current unit inside its column
+  uint32_t seg = 0;       // column segments flushed so far
+  int s = 0;
+  uint32_t ph = 0;
+
+  mbar_wait_backoff(bar_full, 0, 64);  // under PDL this first wait spans the tail of the previous kernel
+  if (threadIdx.x == 0) dbg_stamp1(p, 2);
 
   for (int it = 0; it < my_units; ++it) {
-    const int s = it % STAGES;
-    mbar_wait(bar_full + 8 * s, (it / STAGES) & 1);
-    if (it == 0 && threadIdx.x == 0) dbg_stamp1(p, 2);
+    mbar_wait(bar_full + 8 * s, ph);
 
-    uint32_t s_lo[4], s_hi[4];
+    uint32_t s_lo[Cfg::SG][4], s_hi[Cfg::SG][4];
     if (GROUPED) {
-      const uint4 sv = lds128(sbase + Cfg::OFF_S + s * Cfg::S_STAGE + wn * 128 + g * 16);
-      broadcast_scale_pair(sv.x, s_lo[0], s_hi[0]);
-      broadcast_scale_pair(sv.y, s_lo[1], s_hi[1]);
-      broadcast_scale_pair(sv.z, s_lo[2], s_hi[2]);
-      broadcast_scale_pair(sv.w, s_lo[3], s_hi[3]);
+#pragma unroll
+      for (int gi = 0; gi < Cfg::SG; ++gi) {
+        const uint4 sv = lds128(sbase + Cfg::OFF_S + s * Cfg::S_STAGE + gi * (TN * 2) + s_off);
+        broadcast_scale_pair(sv.x, s_lo[gi][0], s_hi[gi][0]);
+        broadcast_scale_pair(sv.y, s_lo[gi][1], s_hi[gi][1]);
+        broadcast_scale_pair(sv.z, s_lo[gi][2], s_hi[gi][2]);
+        broadcast_scale_pair(sv.w, s_lo[gi][3], s_hi[gi][3]);
+      }
     }
     const uint32_t wst = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
     const uint32_t ast = sbase + Cfg::OFF_A + s * Cfg::A_STAGE;
 
     uint4 q[RPW];
 #pragma unroll
-    for (int i = 0; i < RPW; ++i) {
-      const int r = wk + WK * i;
-      q[i] = lds128(wst + (r * CHUNKS + wn) * 512 + lane * 16);
-    }
+    for (int i = 0; i < RPW; ++i) q[i] = lds128(wst + q_lane + i * (WARPS * 512));
 #pragma unroll
     for (int i = 0; i < RPW; ++i) {
-      const int r = wk + WK * i;  // k16 row inside the stage
       // activation fragments: tokens as the N side of the MMA
       uint32_t bf[NT][2];
-      {
-        const uint32_t sub = ast + (r >> 2) * Cfg::A_SUB;
-        const int c16 = ((r & 3) << 1) + lm_half;
-        if (NT == 1) {
-          const uint32_t addr = sub + lm_row * 128 + ((c16 ^ (lm_row & 7)) << 4);
-          ldmatrix_x2(bf[0][0], bf[0][1], addr);
-        } else {
+      const int RI = WK * i;  // compile-time after unrolling
+      const uint32_t a_row = ast + ((a_lane ^ static_cast<uint32_t>(((RI & 3) << 1) << 4)) +
+                                    static_cast<uint32_t>((RI >> 2) * Cfg::A_SUB));
+      if (NT == 1) {
+        ldmatrix_x2(bf[0][0], bf[0][1], a_row);
+      } else {
 #pragma unroll
-          for (int np = 0; np < NT / 2; ++np) {
-            const int row = np * 16 + lm_row;
-            const uint32_t addr = sub + row * 128 + ((c16 ^ (row & 7)) << 4);
-            ldmatrix_x4(bf[2 * np][0], bf[2 * np][1], bf[2 * np + 1][0], bf[2 * np + 1][1], addr);
-          }
-        }
+        for (int np = 0; np < NT / 2; ++np)  // token rows +16 per pair: 2048 B, swizzle phase unchanged
+          ldmatrix_x4(bf[2 * np][0], bf[2 * np][1], bf[2 * np + 1][0], bf[2 * np + 1][1], a_row + np * 2048);
       }
       const uint32_t qq[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         uint32_t w[4];
-        Dequant<T>::template word<GROUPED>(qq[j], s_lo[j], s_hi[j], w);
+        const int gi = Cfg::SG > 1 ? (RI >> 3) : 0;  // rows 8.. of a two-group stage use the second scale row
+        Dequant<T>::template word<GROUPED>(qq[j], s_lo[gi][j], s_hi[gi][j], w);
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) mma_m16n8k16<T>(acc[j][nt], w, bf[nt][0], bf[nt][1]);
       }
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(bar_empty + 8 * s);
+    if (++s == NS) { s = 0; ph ^= 1u; }
 
-    // ---- end of this CTA's run inside column c?  flush ----
-    const bool last_unit = (it == my_units - 1);
-    if (b == p.kblks - 1 || last_unit) {
-      const int seg_last_b = b;
-      if (threadIdx.x == 0) dbg_stamp1(p, last_unit ? 5 : 3);
-      // 1. reduce the WK warps sharing each chunk through shared memory
+    // ---- end of this CTA's run inside the column?  hand the tile to the flusher ----
+    if (b == p.kblks - 1 || it == my_units - 1) {
+      mbar_wait(bar_red_empty, (seg & 1u) ^ 1u);  // previous tile consumed (passes the first time)
+      // the WK warps sharing a chunk add their partials in wk order (fixed -> deterministic)
 #pragma unroll
       for (int r = 0; r < WK; ++r) {
         if (wk == r) {
@@ -262,93 +390,94 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
               for (int e = 0; e < 4; ++e) {
                 const int n = wn * 64 + j * 16 + g + ((e & 2) ? 8 : 0);
                 const int tok = nt * 8 + 2 * t + (e & 1);
-                float* dst = red + tok * TNP + n;
-                *dst = (r == 0) ? acc[j][nt][e] : (*dst + acc[j][nt][e]);
+                if (tok < p.m) {
+                  float* dst = red + tok * TNP + n;
+                  *dst = (r == 0) ? acc[j][nt][e] : (*dst + acc[j][nt][e]);
+                }
                 acc[j][nt][e] = 0.f;
               }
         }
-        named_bar_sync(1, NCONS);
+        if (r + 1 < WK) named_bar_sync(1, NCONS);
       }
-      const int col0 = c * TN;
-      const int tid = threadIdx.x;
-      const bool whole = (seg_first_b == 0 && seg_last_b == p.kblks - 1);
-
-      // converts 4 fp32 sums to T with the reference's rounding points and stores them
-      auto emit = [&](int tok, int n, float4 v) {
-        T o[4] = {Elem<T>::from_float(v.x), Elem<T>::from_float(v.y), Elem<T>::from_float(v.z),
-                  Elem<T>::from_float(v.w)};
-        if (!GROUPED) {  // channelwise: scale the ROUNDED sum in T (marlin_kernel_impl.cuh:957-963)
-          const T* sc = reinterpret_cast<const T*>(p.scales);
-#pragma unroll
-          for (int e = 0; e < 4; ++e) o[e] = __hmul(o[e], sc[chan_scale_pos(n + e)]);
-        }
-        const size_t off = static_cast<size_t>(tok) * p.n + n;
-        if (p.residual) {
-          const T* rs = reinterpret_cast<const T*>(p.residual) + off;
-#pragma unroll
-          for (int e = 0; e < 4; ++e) o[e] = __hadd(rs[e], o[e]);
-        }
-        if (p.bias) {
-          const T* bs = reinterpret_cast<const T*>(p.bias) + n;
-#pragma unroll
-          for (int e = 0; e < 4; ++e) o[e] = __hadd(o[e], bs[e]);
-        }
-        uint2 pk;
-        pk.x = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[0])) |
-               (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[1])) << 16);
-        pk.y = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[2])) |
-               (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[3])) << 16);
-        *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.c) + off) = pk;
-      };
-
-      if (whole) {
-        for (int e = tid * 4; e < MT * TN; e += NCONS * 4) {
-          const int tok = e / TN, nn = e - tok * TN;
-          if (tok < p.m && col0 + nn < p.n)
-            emit(tok, col0 + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn));
-        }
-      } else {
-        // 2. split column: publish this CTA's fp32 partial, take a ticket, last arrival reduces
-        const long long ufirst = static_cast<long long>(c) * p.kblks;
-        const int cta_first = cta_of_unit(ufirst, units, grid);
-        const int cta_last = cta_of_unit(ufirst + p.kblks - 1, units, grid);
-        const int nparts = cta_last - cta_first + 1;
-        const int my_slot = static_cast<int>(blockIdx.x) - cta_first;
-        float* slots = p.c_tmp + static_cast<size_t>(c) * p.slot_max * p.m * TN;
-        float* mine = slots + static_cast<size_t>(my_slot) * p.m * TN;
-        for (int e = tid * 4; e < p.m * TN; e += NCONS * 4) {
-          const int tok = e / TN, nn = e - tok * TN;
-          __stcg(reinterpret_cast<float4*>(mine + e),
-                 *reinterpret_cast<const float4*>(red + tok * TNP + nn));
-        }
-        __threadfence();
+      if (it == my_units - 1) {
+        // last segment of this CTA: nothing left to overlap with -> all consumer warps finish it
+        if (threadIdx.x == 0) dbg_stamp1(p, 3);
         named_bar_sync(1, NCONS);
-        if (tid == 0) *s_ticket = atomicAdd(p.workspace + c, 1);
-        named_bar_sync(1, NCONS);
-        if (*s_ticket == nparts - 1) {
-          __threadfence();
-          for (int e = tid * 4; e < p.m * TN; e += NCONS * 4) {
-            const int tok = e / TN, nn = e - tok * TN;
-            if (col0 + nn >= p.n) continue;
-            float4 sum = __ldcg(reinterpret_cast<const float4*>(slots + e));
-            for (int sl = 1; sl < nparts; ++sl) {
-              const float4 v =
-                  __ldcg(reinterpret_cast<const float4*>(slots + static_cast<size_t>(sl) * p.m * TN + e));
-              sum.x += v.x;
-              sum.y += v.y;
-              sum.z += v.z;
-              sum.w += v.w;
-            }
-            emit(tok, col0 + nn, sum);
+        pdl_wait_prior_grids();  // C, c_tmp and the flags are shared with prior grids
+        const int c_last = (u1 - 1) / p.kblks;
+        const bool whole = (b == p.kblks - 1) && (u0 <= c_last * p.kblks);  // segment spans the whole column
+        if (threadIdx.x == 0) dbg_stamp1(p, 5);
+        const int tid = static_cast<int>(threadIdx.x);
+        const int items = p.m * (TN / 4);  // float4 items of the valid token rows
+        const int col0 = c_last * TN;
+        if (whole) {
+          for (int e = tid; e < items; e += NCONS) {
+            const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
+            if (col0 + nn < p.n)
+              emit_out<T, GROUPED>(p, tok, col0 + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn));
           }
-          if (tid == 0) p.workspace[c] = 0;  // leave the workspace zeroed (reference contract)
+        } else {
+          const ColumnShare cs = column_share<TN, Cfg::FLAGS_PER_TILE>(p, c_last, units, grid);
+          if (cs.my_slot != 0) {
+            // publisher: fp32 partial -> its c_tmp slot, then st.release of its flag
+            float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
+            for (int e = tid; e < items; e += NCONS) {
+              const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
+              __stcg(reinterpret_cast<float4*>(mine + static_cast<size_t>(e) * 4),
+                     *reinterpret_cast<const float4*>(red + tok * TNP + nn));
+            }
+            named_bar_sync(1, NCONS);  // the release below is cumulative over the stores ordered before it by this barrier
+            if (tid == 0) st_release_gpu(cs.flags + cs.my_slot, 1);
+          } else {
+            // owner: acquire the other flags, pull every partial into the (now dead) weight ring with
+            // all loads in flight at once, add them in slot order, write T, reset the flags
+            const int np1 = cs.nparts - 1;
+            if (tid >= 1 && tid <= np1) {
+              while (ld_acquire_gpu(cs.flags + tid) == 0) {
+              }
+            }
+            named_bar_sync(1, NCONS);
+            if (tid == 0) dbg_stamp1(p, 6);
+            float4* stage = reinterpret_cast<float4*>(smem + Cfg::OFF_W);
+            constexpr int CAP = (NS * Cfg::W_STAGE) / 16;
+            const int ib = CAP / np1;  // items per round
+            for (int i0 = 0; i0 < items; i0 += ib) {
+              const int ni = (items - i0) < ib ? (items - i0) : ib;
+              // fire-and-forget 16-byte copies global(L2) -> shared: every partial of the round in flight at once
+              for (int sl = 0; sl < np1; ++sl) {
+                const float* src = cs.slots + static_cast<size_t>(sl + 1) * cs.slot_elems + static_cast<size_t>(i0) * 4;
+                const uint32_t dst = smem_u32(stage + sl * ni);
+                for (int e = tid; e < ni; e += NCONS)
+                  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + e * 16), "l"(src + e * 4) : "memory");
+              }
+              asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+              named_bar_sync(1, NCONS);
+              for (int e = tid; e < ni; e += NCONS) {
+                const int item = i0 + e;
+                const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
+                if (col0 + nn >= p.n) continue;
+                float4 sum = *reinterpret_cast<const float4*>(red + tok * TNP + nn);
+                for (int sl = 0; sl < np1; ++sl) {
+                  const float4 v = stage[sl * ni + e];
+                  sum.x += v.x;
+                  sum.y += v.y;
+                  sum.z += v.z;
+                  sum.w += v.w;
+                }
+                emit_out<T, GROUPED>(p, tok, col0 + nn, sum);
+              }
+              named_bar_sync(1, NCONS);
+            }
+            if (tid >= 1 && tid <= np1) cs.flags[tid] = 0;  // leave the workspace zeroed (reference contract)
+          }
         }
+        if (threadIdx.x == 0) dbg_stamp1(p, 7);
+      } else {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_red_full);
       }
-      named_bar_sync(1, NCONS);  // `red` and s_ticket are reusable
-      if (threadIdx.x == 0) dbg_stamp1(p, last_unit ? 7 : 4);
-      ++c;
+      ++seg;
       b = 0;
-      seg_first_b = 0;
     } else {
       ++b;
     }

@@ -29,11 +29,11 @@ std::atomic<int> g_default_pdl{[] {
   return (e && e[0] == '1') ? 1 : 0;
 }()};
 
-// which streaming kernel serves M <= 64 by default: 1 = cluster split-K (stream_kernel.cuh),
-// 0 = first generation (decode_kernel.cuh); environment B200_W4A16_STREAM_V2 overrides
+// which streaming kernel serves M <= 32 by default: 0 = persistent stream-K (decode_kernel.cuh),
+// 1 = cluster split-K (stream_kernel.cuh); environment B200_W4A16_STREAM_V2 overrides
 bool g_stream_v2 = [] {
   const char* e = std::getenv("B200_W4A16_STREAM_V2");
-  return e ? (e[0] == '1') : true;
+  return e ? (e[0] == '1') : false;
 }();
 
 // cap on resident CTAs per SM of the first-generation persistent streaming kernel
@@ -185,7 +185,7 @@ int launch_decode(const GemmCall& g) {
   if (GROUPED) {  // scales: T [K/128][N/64][64]
     const uint64_t dims[3] = {64, static_cast<uint64_t>(g.n / 64), static_cast<uint64_t>(g.k / 128)};
     const uint64_t strides[2] = {128, static_cast<uint64_t>(g.n) * 2};
-    const uint32_t box[3] = {64, CHUNKS, 1};
+    const uint32_t box[3] = {64, CHUNKS, static_cast<uint32_t>(Cfg::SG)};
     if (int rc = get_tensor_map(&tm_s, g.scales, Elem<T>::kTmaType, 3, dims, strides, box,
                                 CU_TENSOR_MAP_SWIZZLE_NONE))
       return rc;
@@ -213,7 +213,7 @@ int launch_decode(const GemmCall& g) {
   args.ncols = (g.n + Cfg::TN - 1) / Cfg::TN;
   args.kblks = g.k / Cfg::KB;
   const long long units = static_cast<long long>(args.ncols) * args.kblks;
-  // persistent CTAs: as many per SM as shared memory / registers allow (capped by B200_W4A16_V1_OCC)
+  // persistent CTAs: one per SM (B200_W4A16_V1_OCC raises it for experiments, if resources allow)
   static int occ = 0;
   if (occ == 0) {
     int o = 1;
@@ -221,7 +221,9 @@ int launch_decode(const GemmCall& g) {
     occ = o < g_v1_occ ? o : g_v1_occ;
   }
   const long long slots = static_cast<long long>(sm_count()) * occ;
-  const int grid = static_cast<int>(units < slots ? units : slots);
+  int grid = static_cast<int>(units < slots ? units : slots);
+  // a column may be shared by at most 16 CTAs (flags per column tile in `workspace`, one poller lane each)
+  while (grid > 1 && decode_slot_max(args.kblks, units, grid) > 16) --grid;
   args.slot_max = decode_slot_max(args.kblks, units, grid);
   args.dbg_ts = stream_debug_next_slot();
 
@@ -249,8 +251,9 @@ int launch_decode(const GemmCall& g) {
 // geometry families (id within family = index):  chunks, krows, warps, stages
 #define DECODE_FAMILY(T, DT, NT, GR)                                                    \
   DCFG(T, DT, NT, 2, 8, 8, 8, GR), DCFG(T, DT, NT, 4, 8, 8, 5, GR), DCFG(T, DT, NT, 4, 4, 8, 8, GR), \
-      DCFG(T, DT, NT, 8, 4, 8, 5, GR), DCFG(T, DT, NT, 4, 8, 16, 5, GR), DCFG(T, DT, NT, 2, 8, 16, 8, GR)
-constexpr int kGeoms = 6;
+      DCFG(T, DT, NT, 8, 4, 8, 5, GR), DCFG(T, DT, NT, 4, 8, 16, 5, GR), DCFG(T, DT, NT, 2, 8, 16, 8, GR), \
+      DCFG(T, DT, NT, 2, 16, 8, 5, GR), DCFG(T, DT, NT, 1, 16, 4, 8, GR)
+constexpr int kGeoms = 8;
 
 const DecodeConfig g_decode[] = {
     DECODE_FAMILY(__half, 0, 1, true),          DECODE_FAMILY(__half, 0, 2, true),
@@ -269,19 +272,13 @@ int decode_index(int dtype, int nt, bool grouped, int geom) {
 
 int nt_for_m(int m) { return m <= 8 ? 1 : (m <= 16 ? 2 : 4); }
 
-// shape -> geometry.  Goal: >= ~6 units per CTA for balance, the widest tile that allows it (wide
-// tiles amortise the activation re-reads at M = 16..32), 16 warps when the token tile is small.
+// shape -> geometry of the persistent streaming kernel.  Measured on B200 (profiles/r01): the 256-column
+// x 128-k stage with 8 consumer warps (4 k16-rows per warp and stage) has the fewest instructions per
+// byte and leaves room for the next kernel's CTA on the same SM (PDL); stream-K balances any shape.
 int pick_geometry(int m, int n, int k) {
-  const long long sms = sm_count();
-  auto units = [&](int chunks, int krows) {
-    return static_cast<long long>((n + chunks * 64 - 1) / (chunks * 64)) * (k / (krows * 16));
-  };
-  const bool k128 = (k % 128) == 0;
-  if (k128 && n % 512 == 0 && units(8, 4) >= 12 * sms) return 3;   // tn512 kb64
-  if (k128 && units(4, 8) >= 6 * sms) return 1;                    // tn256 kb128
-  if (units(4, 4) >= 6 * sms) return 2;                            // tn256 kb64
-  if (k128) return 0;                                              // tn128 kb128
-  return 2;
+  (void)m;
+  (void)n;
+  return (k % 128) == 0 ? 1 : 2;  // tn256/kb128/w8, or tn256/kb64/w8 when K is only a multiple of 64
 }
 
 // configuration ids: 1..count = streaming-kernel configurations, kPrefillBase.. = tcgen05 tile shapes
@@ -316,7 +313,7 @@ void prefill_from_id(int id, int* tile, int* S) {
 }
 
 struct Geom { int chunks, krows; };
-const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}};
+const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}, {2, 16}, {1, 16}};
 
 }  // namespace b200
 
