@@ -417,58 +417,144 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
               emit_out<T, GROUPED>(p, tok, col0 + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn));
           }
         } else {
-          const ColumnShare cs = column_share<TN, Cfg::FLAGS_PER_TILE>(p, c_last, units, grid);
-          if (cs.my_slot != 0) {
-            // publisher: fp32 partial -> its c_tmp slot, then st.release of its flag
-            float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
-            for (int e = tid; e < items; e += NCONS) {
-              const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
-              __stcg(reinterpret_cast<float4*>(mine + static_cast<size_t>(e) * 4),
-                     *reinterpret_cast<const float4*>(red + tok * TNP + nn));
+          if (NT == 1) {
+            // few bytes per tile: ONE sharer (the holder of the column's first k-blocks) adds everything;
+            // the others publish and leave
+            const ColumnShare cs = column_share<TN, Cfg::FLAGS_PER_TILE>(p, c_last, units, grid);
+            if (cs.my_slot != 0) {
+              // publisher: fp32 partial -> its c_tmp slot, then st.release of its flag
+              float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
+              for (int e = tid; e < items; e += NCONS) {
+                const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
+                __stcg(reinterpret_cast<float4*>(mine + static_cast<size_t>(e) * 4),
+                       *reinterpret_cast<const float4*>(red + tok * TNP + nn));
+              }
+              named_bar_sync(1, NCONS);  // the release below is cumulative over the stores ordered before it by this barrier
+              if (tid == 0) st_release_gpu(cs.flags + cs.my_slot, 1);
+            } else {
+              // owner: acquire the other flags, pull every partial into the (now dead) weight ring with
+              // all loads in flight at once, add them in slot order, write T, reset the flags
+              const int np1 = cs.nparts - 1;
+              if (tid >= 1 && tid <= np1) {
+                while (ld_acquire_gpu(cs.flags + tid) == 0) {
+                }
+              }
+              named_bar_sync(1, NCONS);
+              if (tid == 0) dbg_stamp1(p, 6);
+              float4* stage = reinterpret_cast<float4*>(smem + Cfg::OFF_W);
+              constexpr int CAP = (NS * Cfg::W_STAGE) / 16;
+              const int ib = CAP / np1;  // items per round
+              for (int i0 = 0; i0 < items; i0 += ib) {
+                const int ni = (items - i0) < ib ? (items - i0) : ib;
+                // fire-and-forget 16-byte copies global(L2) -> shared: every partial of the round in flight at once
+                for (int sl = 0; sl < np1; ++sl) {
+                  const float* src = cs.slots + static_cast<size_t>(sl + 1) * cs.slot_elems + static_cast<size_t>(i0) * 4;
+                  const uint32_t dst = smem_u32(stage + sl * ni);
+                  for (int e = tid; e < ni; e += NCONS)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + e * 16), "l"(src + e * 4) : "memory");
+                }
+                asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+                named_bar_sync(1, NCONS);
+                for (int e = tid; e < ni; e += NCONS) {
+                  const int item = i0 + e;
+                  const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
+                  if (col0 + nn >= p.n) continue;
+                  float4 sum = *reinterpret_cast<const float4*>(red + tok * TNP + nn);
+                  for (int sl = 0; sl < np1; ++sl) {
+                    const float4 v = stage[sl * ni + e];
+                    sum.x += v.x;
+                    sum.y += v.y;
+                    sum.z += v.z;
+                    sum.w += v.w;
+                  }
+                  emit_out<T, GROUPED>(p, tok, col0 + nn, sum);
+                }
+                named_bar_sync(1, NCONS);
+              }
+              if (tid >= 1 && tid <= np1) cs.flags[tid] = 0;  // leave the workspace zeroed (reference contract)
             }
-            named_bar_sync(1, NCONS);  // the release below is cumulative over the stores ordered before it by this barrier
-            if (tid == 0) st_release_gpu(cs.flags + cs.my_slot, 1);
           } else {
-            // owner: acquire the other flags, pull every partial into the (now dead) weight ring with
-            // all loads in flight at once, add them in slot order, write T, reset the flags
-            const int np1 = cs.nparts - 1;
-            if (tid >= 1 && tid <= np1) {
+            // A split column, and this is the last segment of this CTA.  Every sharer whose segment is its
+            // last one ("late": all but possibly the sharer holding the column's final k-blocks, which
+            // published early through its flusher) takes an equal slice of the tile: publish the own
+            // partial, acquire everybody's flag, pull the other partials of the slice into the (now dead)
+            // weight ring with all copies in flight at once, add them in slot order, write T.  The late
+            // sharer that finishes last (counter) resets the flags: the workspace goes back to zero.
+            const ColumnShare cs = column_share<TN, Cfg::FLAGS_PER_TILE>(p, c_last, units, grid);
+            const int col_end = (c_last + 1) * p.kblks;
+            const int last_sharer_end = unit_begin(static_cast<int>(blockIdx.x) - cs.my_slot + cs.nparts, units, grid);
+            const int nlate = cs.nparts - (last_sharer_end > col_end ? 1 : 0);
+            int* done = cs.flags + 15;  // flags 0..14 + counter: inside the first 16 ints of the tile, always in bounds
+            {
+              float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
+              for (int e = tid; e < items; e += NCONS) {
+                const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
+                __stcg(reinterpret_cast<float4*>(mine + static_cast<size_t>(e) * 4),
+                       *reinterpret_cast<const float4*>(red + tok * TNP + nn));
+              }
+              named_bar_sync(1, NCONS);  // the release below is cumulative over the stores ordered before it by this barrier
+              if (tid == 0) st_release_gpu(cs.flags + cs.my_slot, 1);
+            }
+            if (tid < cs.nparts && tid != cs.my_slot) {
               while (ld_acquire_gpu(cs.flags + tid) == 0) {
               }
             }
             named_bar_sync(1, NCONS);
             if (tid == 0) dbg_stamp1(p, 6);
-            float4* stage = reinterpret_cast<float4*>(smem + Cfg::OFF_W);
-            constexpr int CAP = (NS * Cfg::W_STAGE) / 16;
-            const int ib = CAP / np1;  // items per round
-            for (int i0 = 0; i0 < items; i0 += ib) {
-              const int ni = (items - i0) < ib ? (items - i0) : ib;
-              // fire-and-forget 16-byte copies global(L2) -> shared: every partial of the round in flight at once
-              for (int sl = 0; sl < np1; ++sl) {
-                const float* src = cs.slots + static_cast<size_t>(sl + 1) * cs.slot_elems + static_cast<size_t>(i0) * 4;
-                const uint32_t dst = smem_u32(stage + sl * ni);
-                for (int e = tid; e < ni; e += NCONS)
-                  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + e * 16), "l"(src + e * 4) : "memory");
-              }
-              asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
-              named_bar_sync(1, NCONS);
-              for (int e = tid; e < ni; e += NCONS) {
-                const int item = i0 + e;
-                const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
-                if (col0 + nn >= p.n) continue;
-                float4 sum = *reinterpret_cast<const float4*>(red + tok * TNP + nn);
-                for (int sl = 0; sl < np1; ++sl) {
-                  const float4 v = stage[sl * ni + e];
-                  sum.x += v.x;
-                  sum.y += v.y;
-                  sum.z += v.z;
-                  sum.w += v.w;
+            {
+              const int e_lo = static_cast<int>((static_cast<long long>(cs.my_slot) * items) / nlate);
+              const int e_hi = static_cast<int>((static_cast<long long>(cs.my_slot + 1) * items) / nlate);
+              const int np1 = cs.nparts - 1;
+              float4* stage = reinterpret_cast<float4*>(smem + Cfg::OFF_W);
+              constexpr int CAP = (NS * Cfg::W_STAGE) / 16;
+              const int ib = CAP / np1;  // items per round
+              for (int i0 = e_lo; i0 < e_hi; i0 += ib) {
+                const int ni = (e_hi - i0) < ib ? (e_hi - i0) : ib;
+                // fire-and-forget 16-byte copies global(L2) -> shared, the own slot skipped
+                for (int sl = 0, row = 0; sl < cs.nparts; ++sl) {
+                  if (sl == cs.my_slot) continue;
+                  const float* src = cs.slots + static_cast<size_t>(sl) * cs.slot_elems + static_cast<size_t>(i0) * 4;
+                  const uint32_t dst = smem_u32(stage + row * ni);
+                  for (int e = tid; e < ni; e += NCONS)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + e * 16), "l"(src + e * 4) : "memory");
+                  ++row;
                 }
-                emit_out<T, GROUPED>(p, tok, col0 + nn, sum);
+                asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+                named_bar_sync(1, NCONS);
+                for (int e = tid; e < ni; e += NCONS) {
+                  const int item = i0 + e;
+                  const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
+                  if (col0 + nn >= p.n) continue;
+                  const float4 own = *reinterpret_cast<const float4*>(red + tok * TNP + nn);
+                  float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+                  for (int sl = 0, row = 0; sl < cs.nparts; ++sl) {  // slot order: bit-deterministic
+                    float4 v;
+                    if (sl == cs.my_slot) {
+                      v = own;
+                    } else {
+                      v = stage[row * ni + e];
+                      ++row;
+                    }
+                    if (sl == 0) {
+                      sum = v;
+                    } else {
+                      sum.x += v.x;
+                      sum.y += v.y;
+                      sum.z += v.z;
+                      sum.w += v.w;
+                    }
+                  }
+                  emit_out<T, GROUPED>(p, tok, col0 + nn, sum);
+                }
+                named_bar_sync(1, NCONS);
               }
-              named_bar_sync(1, NCONS);
             }
-            if (tid >= 1 && tid <= np1) cs.flags[tid] = 0;  // leave the workspace zeroed (reference contract)
+            if (tid == 0) {
+              if (atomicAdd(done, 1) == nlate - 1) {  // every late sharer has read the flags and the partials
+                for (int sl = 0; sl < cs.nparts; ++sl) cs.flags[sl] = 0;
+                *done = 0;  // leave the workspace zeroed (reference contract)
+              }
+            }
           }
         }
         if (threadIdx.x == 0) dbg_stamp1(p, 7);

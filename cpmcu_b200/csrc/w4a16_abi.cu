@@ -222,8 +222,9 @@ int launch_decode(const GemmCall& g) {
   }
   const long long slots = static_cast<long long>(sm_count()) * occ;
   int grid = static_cast<int>(units < slots ? units : slots);
-  // a column may be shared by at most 16 CTAs (flags per column tile in `workspace`, one poller lane each)
-  while (grid > 1 && decode_slot_max(args.kblks, units, grid) > 16) --grid;
+  // a column may be shared by at most 15 CTAs (16 ints of `workspace` per 64 columns: one flag per
+  // sharer + the completion counter)
+  while (grid > 1 && decode_slot_max(args.kblks, units, grid) > 15) --grid;
   args.slot_max = decode_slot_max(args.kblks, units, grid);
   args.dbg_ts = stream_debug_next_slot();
 
