@@ -370,12 +370,19 @@ def main():
     low = [m for m in widths if m <= 32] or widths
     low_ms = sum(per_width_ms[m] for m in low)
     achieved = pass_bytes * len(low) / (low_ms * 1e-3) / 1e9
+    traffic, traffic_note = None, ""
+    tpath = os.path.join(ROOT, "profiles", "r01", "d_traffic.json")
+    if not use_ref_kernel and os.path.exists(tpath):  # DRAM bytes of the dominant launch from the committed ncu capture
+        tj = json.load(open(tpath))
+        traffic = tj["traffic"]
+        traffic_note = (f"; traffic = ncu dram read+write bytes of one {tj['launch']} launch "
+                        f"(algorithmic {tj['algorithmic_bytes']} B)")
     roofline = dict(bound="hbm", achieved=round(achieved, 1), peak=pk["hbm"], unit="GB/s",
-                    frac=round(achieved / pk["hbm"], 4), traffic=None,
+                    frac=round(achieved / pk["hbm"], 4), traffic=traffic,
                     kernel="w4a16_decode_kernel" if not use_ref_kernel else "marlin::Marlin",
                     note=f"all launches at widths {low}: algorithmic weight+scale bytes / summed device time of "
                          f"those passes (back-to-back launches, gaps charged to the kernel); peak = {pk['source']}; "
-                         f"frac of nominal 8000 GB/s = {achieved / 8000.0:.4f}")
+                         f"frac of nominal 8000 GB/s = {achieved / 8000.0:.4f}" + traffic_note)
 
     value = step_bytes / (ms_per_step * 1e-3) / 1e9
     e2e_value = step_bytes / (e2e_ms * 1e-3) / 1e9
