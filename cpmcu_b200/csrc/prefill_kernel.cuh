@@ -49,7 +49,12 @@ struct PrefillCfg {
   // A/W rings, which are dead once the last MMA of the CTA's only tile has been committed
   static constexpr int RED_PITCH = 128 + 4;
   static constexpr int RED_BYTES = SPLIT ? BM * RED_PITCH * 4 : 0;
-  static constexpr int WPC = DW / CHUNKS;          // dequant warps sharing a chunk
+  // dequant warps work in DGROUPS groups that take alternate k-blocks (group g: every k-block whose
+  // running index has parity g), so a warp converts more k16-rows per barrier round trip
+  static constexpr int DGROUPS =
+      ((DW / 2) >= CHUNKS && (DW / 2) % CHUNKS == 0 && STAGES % 2 == 0 && QSTAGES % 2 == 0) ? 2 : 1;
+  static constexpr int DWG = DW / DGROUPS;         // dequant warps per group = arrivals per stage
+  static constexpr int WPC = DWG / CHUNKS;         // dequant warps of a group sharing a chunk
   static constexpr int RPW = 4 / WPC;              // k16-rows per dequant warp per stage
   static constexpr int OFF_A = 0;
   static constexpr int OFF_W = OFF_A + STAGES * A_STAGE;
@@ -59,7 +64,8 @@ struct PrefillCfg {
   static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4;
   static constexpr int SMEM_BYTES = OFF_BAR + NBARS * 8 + 16 + 1024;  // +1024: manual alignment
   static constexpr int THREADS = (7 + DW) * 32;
-  static_assert(DW % CHUNKS == 0 && WPC >= 1 && 4 % WPC == 0, "dequant warp layout");
+  static_assert(DWG % CHUNKS == 0 && WPC >= 1 && 4 % WPC == 0, "dequant warp layout");
+  static_assert(DGROUPS == 1 || (STAGES % 2 == 0 && QSTAGES % 2 == 0), "two dequant groups walk the rings with stride 2");
   static_assert(TMEM_COLS >= 32 && TMEM_COLS <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "tensor memory allocation");
   static_assert(!SPLIT || (NSUB == 1 && RED_BYTES <= OFF_BAR), "split-K staging must fit in the dead rings (A, W and Q are all drained when the accumulator is complete)");
   static_assert(BM % 16 == 0 && BM <= 256, "UMMA N");
@@ -94,13 +100,13 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(bar_a_full + 8 * s, 1);
-      mbar_init(bar_w_full + 8 * s, DW);
+      mbar_init(bar_w_full + 8 * s, Cfg::DWG);
       mbar_init(bar_consumed + 8 * s, 1);
     }
 #pragma unroll
     for (int s = 0; s < QSTAGES; ++s) {
       mbar_init(bar_q_full + 8 * s, 1);
-      mbar_init(bar_q_empty + 8 * s, DW);
+      mbar_init(bar_q_empty + 8 * s, Cfg::DWG);
     }
 #pragma unroll
     for (int a = 0; a < 2; ++a) {
@@ -115,8 +121,10 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // PDL: the next kernel may start its prologue now; of THIS kernel only the activation producer and
+  // the epilogue touch memory the prior grid writes (A, C, residual), so only they wait for it — the
+  // int4 stream, the dequantisers and the W ring run ahead during the previous kernel's tail
   pdl_launch_dependents();
-  pdl_wait_prior_grids();
 
   const int total_tiles = p.n_tiles * p.m_tiles;
   // work items: persistent walk over whole-K tiles, or (split-K) exactly one tile and one K slice
@@ -136,6 +144,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
     // ============================== TMA producer: activations (ring A) ==============================
     if (lane == 0) {
       tma_prefetch_desc(&tm_a);
+      pdl_wait_prior_grids();
       int it = 0;
       for (int tile = tile_begin; tile < total_tiles; tile += tile_step) {
         const int mt = tile % p.m_tiles;
@@ -209,69 +218,76 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
   } else if (warp >= 7) {
     // ====================================== dequantisers ======================================
     const int d = warp - 7;
-    const int ch = d % CHUNKS;      // 64-column chunk of the tile
-    const int rp = d / CHUNKS;      // k16-row phase
+    const int grp = d / Cfg::DWG;   // dequant group: takes the k-blocks whose running index has this parity
+    const int dl = d % Cfg::DWG;
+    const int ch = dl % CHUNKS;     // 64-column chunk of the tile
+    const int rp = dl / CHUNKS;     // k16-row phase
     const int g = lane >> 2;
-    // stmatrix row address of this lane for word j of k16-row r:
+    // stmatrix row address of this lane for word j of k16-row r = rp | WPC*i:
     //   matrix (lane>>3): rows +8 for odd matrices, k half (lane>>4); row low bits = lane & 7
+    //   tile row nrow = ch*64 + j*16 + lrow -> (nrow>>7)*16384 + (nrow&127)*128, 16-byte k chunk
+    //   c16 = 2r + lkh XOR-swizzled with nrow&7 = lrow&7: a lane constant, XOR (2*WPC*i)<<4, plus j*2048
     const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8;
     const int lkh = lane >> 4;
-    int it = 0;
-    for (int tile = tile_begin; tile < total_tiles; tile += tile_step) {
-      for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
-        const int sq = it % QSTAGES;
-        mbar_wait(bar_q_full + 8 * sq, (it / QSTAGES) & 1);
-        uint32_t s_lo[4] = {0, 0, 0, 0}, s_hi[4] = {0, 0, 0, 0};
-        if (GROUPED) {
-          const uint4 sv = lds128(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE + ch * 128 + g * 16);
-          broadcast_scale_pair(sv.x, s_lo[0], s_hi[0]);
-          broadcast_scale_pair(sv.y, s_lo[1], s_hi[1]);
-          broadcast_scale_pair(sv.z, s_lo[2], s_hi[2]);
-          broadcast_scale_pair(sv.w, s_lo[3], s_hi[3]);
-        }
-        uint4 q[Cfg::RPW];
+    const uint32_t w_lane = static_cast<uint32_t>((ch >> 1) * 16384 + ((ch & 1) * 64 + lrow) * 128 +
+                                                  ((((2 * rp) | lkh) ^ (lrow & 7)) << 4));
+    const uint32_t q_lane = static_cast<uint32_t>((rp * CHUNKS + ch) * 512 + lane * 16);
+    const uint32_t s_lane = static_cast<uint32_t>(ch * 128 + g * 16);
+    int my_tiles = 0;
+    for (int tile = tile_begin; tile < total_tiles; tile += tile_step) ++my_tiles;
+    const int total_its = my_tiles * (kb_hi - kb_lo);
+    int sq = grp % QSTAGES, s = grp % STAGES;
+    uint32_t qph = 0, wph = 1;  // parities: raw slot filled; W slot drained (passes the first lap)
+    for (int it = grp; it < total_its; it += Cfg::DGROUPS) {
+      mbar_wait(bar_q_full + 8 * sq, qph);
+      uint32_t s_lo[4] = {0, 0, 0, 0}, s_hi[4] = {0, 0, 0, 0};
+      if (GROUPED) {
+        const uint4 sv = lds128(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE + s_lane);
+        broadcast_scale_pair(sv.x, s_lo[0], s_hi[0]);
+        broadcast_scale_pair(sv.y, s_lo[1], s_hi[1]);
+        broadcast_scale_pair(sv.z, s_lo[2], s_hi[2]);
+        broadcast_scale_pair(sv.w, s_lo[3], s_hi[3]);
+      }
+      uint4 q[Cfg::RPW];
 #pragma unroll
-        for (int i = 0; i < Cfg::RPW; ++i) {
-          const int r = rp + Cfg::WPC * i;
-          q[i] = lds128(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE + (r * CHUNKS + ch) * 512 + lane * 16);
-        }
-        // the slot may be overwritten by TMA as soon as it is released: make the release wait for the
-        // LDS results (an arrive has no data dependency on outstanding loads by itself)
+      for (int i = 0; i < Cfg::RPW; ++i)
+        q[i] = lds128(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE + q_lane + i * (Cfg::WPC * CHUNKS * 512));
+      // the slot may be overwritten by TMA as soon as it is released: make the release wait for the
+      // LDS results (an arrive has no data dependency on outstanding loads by itself)
 #pragma unroll
-        for (int i = 0; i < Cfg::RPW; ++i)
-          asm volatile("" ::"r"(q[i].x), "r"(q[i].y), "r"(q[i].z), "r"(q[i].w) : "memory");
-        asm volatile("" ::"r"(s_lo[0]), "r"(s_lo[1]), "r"(s_lo[2]), "r"(s_lo[3]) : "memory");
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);  // raw slot is in registers now
+      for (int i = 0; i < Cfg::RPW; ++i)
+        asm volatile("" ::"r"(q[i].x), "r"(q[i].y), "r"(q[i].z), "r"(q[i].w) : "memory");
+      asm volatile("" ::"r"(s_lo[0]), "r"(s_lo[1]), "r"(s_lo[2]), "r"(s_lo[3]) : "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);  // raw slot is in registers now
 
-        const int s = it % STAGES;
-        mbar_wait(bar_consumed + 8 * s, ((it / STAGES) & 1) ^ 1);  // W slot drained by the tensor core
-        const uint32_t w_addr = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
-        if (!(p.dbg & 1))
+      mbar_wait(bar_consumed + 8 * s, wph);  // W slot drained by the tensor core
+      const uint32_t w_addr = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
+      if (!(p.dbg & 1))
 #pragma unroll
         for (int i = 0; i < Cfg::RPW; ++i) {
-          const int r = rp + Cfg::WPC * i;
           const uint32_t qq[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
+          const uint32_t row_addr = w_addr + (w_lane ^ static_cast<uint32_t>((2 * Cfg::WPC * i) << 4));
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint32_t w[4];
             Dequant<T>::template word<GROUPED>(qq[j], s_lo[j], s_hi[j], w);
             // w[0]: n=g, k 0..7 | w[1]: n=g+8, k 0..7 | w[2]: n=g, k 8..15 | w[3]: n=g+8, k 8..15
-            const int nrow = ch * 64 + j * 16 + lrow;     // row of the CTA tile this lane addresses
-            const int c16 = 2 * r + lkh;                  // 16-byte k chunk inside the 128-byte row
-            const uint32_t addr = w_addr + (nrow >> 7) * 16384 + (nrow & 127) * 128 +
-                                  ((c16 ^ (nrow & 7)) << 4);
-            stmatrix_x4(addr, w[0], w[1], w[2], w[3]);
+            stmatrix_x4(row_addr + j * 2048, w[0], w[1], w[2], w[3]);
           }
         }
-        fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_w_full + 8 * s);
-      }
+      fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_w_full + 8 * s);
+      sq += Cfg::DGROUPS;
+      if (sq >= QSTAGES) { sq -= QSTAGES; qph ^= 1u; }
+      s += Cfg::DGROUPS;
+      if (s >= STAGES) { s -= STAGES; wph ^= 1u; }
     }
   } else {
     // ======================================== epilogue ========================================
     const int qd = warp;  // TMEM lane quarter: this warp may touch lanes 32*qd .. 32*qd+31
+    pdl_wait_prior_grids();
     int acc_it = 0;
     for (int tile = tile_begin; tile < total_tiles; tile += tile_step, ++acc_it) {
       const int mt = tile % p.m_tiles, nt = tile / p.m_tiles;

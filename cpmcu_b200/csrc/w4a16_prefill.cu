@@ -18,10 +18,11 @@ struct TileShape {
   const char* name;
 };
 const TileShape kTiles[kPrefillTiles] = {
-    {2, 256, 1.00f, "tc/bn256/bm256"},
-    {1, 256, 0.95f, "tc/bn128/bm256"},
-    {2, 128, 0.85f, "tc/bn256/bm128"},
-    {1, 128, 0.75f, "tc/bn128/bm128"},
+    // weights: measured relative throughput on B200 at M = 4096 (profiles/r01, 8 dequant warps per CTA)
+    {2, 256, 0.83f, "tc/bn256/bm256"},
+    {1, 256, 1.00f, "tc/bn128/bm256"},
+    {2, 128, 0.73f, "tc/bn256/bm128"},
+    {1, 128, 0.66f, "tc/bn128/bm128"},
     // split-K over a thread-block cluster (mid M: the N x M grid alone cannot fill the machine)
     {1, 64, 0.f, "tc/bn128/bm64/splitk"},
     {1, 128, 0.f, "tc/bn128/bm128/splitk"},
@@ -145,10 +146,10 @@ int launch_one(const GemmCall& g, int S, int* query) {
 template <typename T, bool GROUPED>
 int launch_tile(const GemmCall& g, int tile, int S, int* query) {
   switch (tile) {
-    case 0: return launch_one<T, 2, 256, 3, 3, 4, GROUPED, false>(g, 1, query);
-    case 1: return launch_one<T, 1, 256, 4, 4, 4, GROUPED, false>(g, 1, query);
+    case 0: return launch_one<T, 2, 256, 3, 3, 8, GROUPED, false>(g, 1, query);
+    case 1: return launch_one<T, 1, 256, 4, 4, 8, GROUPED, false>(g, 1, query);
     case 2: return launch_one<T, 2, 128, 4, 3, 8, GROUPED, false>(g, 1, query);
-    case 3: return launch_one<T, 1, 128, 6, 6, 4, GROUPED, false>(g, 1, query);
+    case 3: return launch_one<T, 1, 128, 6, 6, 8, GROUPED, false>(g, 1, query);
     case 4: return launch_one<T, 1, 64, 2, 10, 8, GROUPED, true>(g, S, query);
     case 5: return launch_one<T, 1, 128, 2, 8, 8, GROUPED, true>(g, S, query);
   }
