@@ -211,6 +211,8 @@ def main():
     ap.add_argument("--no-detail", action="store_true")
     ap.add_argument("--workload", default="auto", choices=["auto", "minicpm4", "llama70b"],
                     help="auto: MiniCPM4-8B linears at N=1, tensor-parallel Llama-3-70B linears at N>1")
+    ap.add_argument("--collective", default="oneshot", choices=["oneshot", "nccl"],
+                    help="all-reduce after the row-parallel linears (N > 1): this library's one-shot NVLink kernel, or NCCL")
     ap.add_argument("--tp-layers", type=int, default=16)
     ap.add_argument("--tp-widths", default="1,16,64")
     args = ap.parse_args()

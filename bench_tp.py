@@ -88,21 +88,50 @@ def main_tp(args, rank, world, local_rank, use_reference=False):
     c_tmp = torch.empty(scratch + 64, dtype=torch.float32, device=dev)
     n_launch = [0]
 
-    def gemm(i, l, m):
+    # the collective after the row-parallel linears: this library's one-shot NVLink all-reduce over
+    # symmetric (peer-mapped) buffers; NCCL all-reduce if symmetric memory is unavailable or --collective nccl
+    ar = None
+    collective = "none"
+    if eff_world > 1:
+        collective = "NCCL all-reduce (fp16, sum) inside the CUDA graph"
+        if getattr(args, "collective", "oneshot") == "oneshot":
+            try:
+                from cpmcu_b200.collective import OneShotAllReduce
+                ar = OneShotAllReduce(max(widths) * max(d["n"] for d in lins if d["style"] == "row"),
+                                      torch.float16, dev)
+                collective = ("one-shot all-reduce kernel of this library over NVLink peer memory "
+                              "(b200_w4a16_allreduce_oneshot; fp32 sum in rank order), inside the CUDA graph")
+            except Exception as e:  # noqa: BLE001
+                sys.stderr.write(f"[rank {rank}] symmetric memory unavailable ({e!r}); using NCCL all-reduce\n")
+                ar = None
+        flag = torch.tensor([1 if ar is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)   # every rank must take the same path
+        if int(flag.item()) == 0:
+            ar, collective = None, "NCCL all-reduce (fp16, sum) inside the CUDA graph"
+
+    def gemm(i, l, m, out):
         d = lins[i]
         if use_reference:
-            ref_marlin.gemm(acts[m][i], d["q"][l], d["s"][l], d["ws"], c_tmp, out=outs[m][i], stream=stream)
+            ref_marlin.gemm(acts[m][i], d["q"][l], d["s"][l], d["ws"], c_tmp, out=out, stream=stream)
         else:
-            B.gemm(acts[m][i], d["q"][l], d["s"][l], d["ws"], c_tmp, out=outs[m][i], pdl=not args.no_pdl,
+            B.gemm(acts[m][i], d["q"][l], d["s"][l], d["ws"], c_tmp, out=out, pdl=not args.no_pdl,
                    stream=stream)
         n_launch[0] += 1
 
     def one_pass(m, comm=True, compute=True):
         for l in range(L):
             for i, d in enumerate(lins):
+                reduce_here = comm and d["style"] == "row" and eff_world > 1
+                if reduce_here and ar is not None:
+                    buf = ar.next_input(m, d["n"])      # the GEMM writes its partial into the symmetric buffer
+                    if compute:
+                        gemm(i, l, m, buf)
+                    ar.reduce(buf, outs[m][i], stream=stream)
+                    n_launch[0] += 1
+                    continue
                 if compute:
-                    gemm(i, l, m)
-                if comm and d["style"] == "row" and eff_world > 1:
+                    gemm(i, l, m, outs[m][i])
+                if reduce_here:
                     dist.all_reduce(outs[m][i])
 
     def capture(m, comm=True, compute=True):
@@ -196,8 +225,7 @@ def main_tp(args, rank, world, local_rank, use_reference=False):
         "config": {"workload": f"Llama-3-70B W4A16 linears (qkv 8192x10240 col, o 8192x8192 row+allreduce, gate_up "
                                f"8192x57344 col, down 28672x8192 row+allreduce; group 128) x {L} layers at widths "
                                f"M={widths}, tensor-parallel over {eff_world} GPU(s)",
-                   "parallelism": f"tp{eff_world}", "collective": "NCCL all-reduce (fp16, sum) inside the CUDA graph"
-                   if eff_world > 1 else "none",
+                   "parallelism": f"tp{eff_world}", "collective": collective,
                    "l2": f"inputs larger than L2: {local_bytes / 2**30:.2f} GiB of weights per GPU per width",
                    "impl": "reference Marlin, unsharded on one GPU (the reference has no multi-GPU path)"
                    if use_reference else "cpmcu_b200 (sm_100a)"},
@@ -207,7 +235,7 @@ def main_tp(args, rank, world, local_rank, use_reference=False):
         "gpu_launches": launches_per_step * K * eff_world,
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": round(peak, 1), "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "traffic": None,
-                     "kernel": "marlin::Marlin" if use_reference else "w4a16_stream_kernel",
+                     "kernel": "marlin::Marlin" if use_reference else "w4a16_decode_kernel",
                      "note": f"widths {low}: whole-model algorithmic bytes / max-over-ranks device time; peak = "
                              f"{eff_world} x {pk['hbm']} GB/s ({pk['source']})"},
         "clocks": clocks,

@@ -100,6 +100,19 @@ int b200_w4a16_dequant(const int32_t* qweight, const void* scales, void* w_out, 
 int b200_w4a16_repack_gptq(const int32_t* qweight_gptq, int32_t* qweight_marlin, int64_t n, int64_t k,
                            void* stream);
 
+/* One-shot all-reduce (sum, in rank order, fp32 accumulate) of the [M][N] partial outputs of a
+ * row-parallel linear (o / down sharded along K) over NVLink peer memory — the collective that follows
+ * the GEMM when the path is sharded (the reference has no multi-GPU code).
+ *   peer_in[w]   HOST array of `world` device pointers: rank w's symmetric input buffer T[elems], mapped
+ *                into this process (e.g. torch.distributed._symmetric_memory buffer_ptrs)
+ *   peer_sig[w]  HOST array of `world` device pointers: rank w's signal pad, int32[128][8], zero-initialised
+ *   epoch        local device int32[128], zero-initialised, private to this (buffer, signal pad) pair
+ *   out          local T[elems]; elems a multiple of 8
+ * Every rank must call it the same number of times in the same order; callers alternate between two
+ * (input buffer) sets so that no trailing barrier is needed.  Graph-capturable. */
+int b200_w4a16_allreduce_oneshot(const void* const* peer_in, int32_t* const* peer_sig, int32_t* epoch,
+                                 void* out, int64_t elems, int dtype, int rank, int world, void* stream);
+
 /* Process-wide default for programmatic dependent launch on entry points that take no opts
  * (b200_w4a16_gemm, b200_w4a16_linear_forward): 1 = every GEMM launch carries the PDL attribute so
  * its weight prefetch overlaps the tail of the previous kernel in the stream (safe with any
