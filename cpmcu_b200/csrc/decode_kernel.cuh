@@ -153,7 +153,7 @@ __device__ __forceinline__ ColumnShare column_share(const DecodeArgs& p, int c, 
 }
 
 template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED>
-__global__ void __launch_bounds__(WARPS * 32 + 64, (NT == 1 || (NT == 2 && WARPS <= 8)) ? 2 : 1)
+__global__ void __launch_bounds__(WARPS * 32 + 64, (NT == 1 || (NT == 2 && WARPS <= 8)) ? 2 : 1)  // 2: PDL co-residency
 w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_s,
                     const __grid_constant__ CUtensorMap tm_a, const DecodeArgs p) {
   using Cfg = DecodeCfg<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>;

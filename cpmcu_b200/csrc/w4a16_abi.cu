@@ -253,8 +253,8 @@ int launch_decode(const GemmCall& g) {
 #define DECODE_FAMILY(T, DT, NT, GR)                                                    \
   DCFG(T, DT, NT, 2, 8, 8, 8, GR), DCFG(T, DT, NT, 4, 8, 8, 5, GR), DCFG(T, DT, NT, 4, 4, 8, 8, GR), \
       DCFG(T, DT, NT, 8, 4, 8, 5, GR), DCFG(T, DT, NT, 4, 8, 16, 5, GR), DCFG(T, DT, NT, 2, 8, 16, 8, GR), \
-      DCFG(T, DT, NT, 2, 16, 8, 5, GR), DCFG(T, DT, NT, 1, 16, 4, 8, GR)
-constexpr int kGeoms = 8;
+      DCFG(T, DT, NT, 2, 16, 8, 5, GR), DCFG(T, DT, NT, 1, 16, 4, 8, GR), DCFG(T, DT, NT, 3, 16, 12, 3, GR)
+constexpr int kGeoms = 9;
 
 const DecodeConfig g_decode[] = {
     DECODE_FAMILY(__half, 0, 1, true),          DECODE_FAMILY(__half, 0, 2, true),
@@ -314,7 +314,7 @@ void prefill_from_id(int id, int* tile, int* S) {
 }
 
 struct Geom { int chunks, krows; };
-const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}, {2, 16}, {1, 16}};
+const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}, {2, 16}, {1, 16}, {3, 16}};
 
 }  // namespace b200
 
