@@ -65,6 +65,8 @@ SYMBOLS = {
     "b200_w4a16_debug_timeline": (None, [c_void_p, c_int64]),
     "b200_w4a16_allreduce_oneshot": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                                              c_void_p]),
+    "b200_w4a16_allreduce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
+                                     c_int, c_void_p]),
 }
 
 

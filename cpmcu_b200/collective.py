@@ -42,19 +42,23 @@ class OneShotAllReduce:
         max_elems = (max_elems + 7) // 8 * 8
         self.max_elems, self.dtype, self.device = max_elems, dtype, device
         self.data = symm.empty((2, max_elems), dtype=dtype, device=device)
-        self.sig = symm.empty((2, MAX_BLOCKS * MAX_WORLD), dtype=torch.int32, device=device)
+        self.res = symm.empty((2, max_elems), dtype=dtype, device=device)   # two-shot result slices
+        self.sig = symm.empty((2, 2 * MAX_BLOCKS * MAX_WORLD), dtype=torch.int32, device=device)
         self.data.zero_()
+        self.res.zero_()
         self.sig.zero_()
         torch.cuda.synchronize(device)
         hd = symm.rendezvous(self.data, gname)
+        hr = symm.rendezvous(self.res, gname)
         hs = symm.rendezvous(self.sig, gname)
         dist.barrier(self.group)
         esz = self.data.element_size()
         PtrArr = ctypes.c_void_p * self.world
         self._in = [PtrArr(*[int(p) + i * max_elems * esz for p in hd.buffer_ptrs]) for i in range(2)]
-        self._sig = [PtrArr(*[int(p) + i * MAX_BLOCKS * MAX_WORLD * 4 for p in hs.buffer_ptrs]) for i in range(2)]
-        self.epoch = torch.zeros((2, MAX_BLOCKS), dtype=torch.int32, device=device)
-        self._handles = (hd, hs)
+        self._res = [PtrArr(*[int(p) + i * max_elems * esz for p in hr.buffer_ptrs]) for i in range(2)]
+        self._sig = [PtrArr(*[int(p) + i * 2 * MAX_BLOCKS * MAX_WORLD * 4 for p in hs.buffer_ptrs]) for i in range(2)]
+        self.epoch = torch.zeros((2, 2 * MAX_BLOCKS), dtype=torch.int32, device=device)
+        self._handles = (hd, hr, hs)
         self._turn = 0
 
     def next_input(self, m: int, n: int):
@@ -62,14 +66,18 @@ class OneShotAllReduce:
         assert m * n <= self.max_elems
         return self.data[self._turn, : m * n].view(m, n)
 
-    def reduce(self, buf, out, stream=None):
+    def reduce(self, buf, out, stream=None, two_shot=None):
         i = self._turn
         assert buf.data_ptr() == self.data[i].data_ptr(), "reduce() must be given the buffer of next_input()"
         elems = buf.numel()
-        rc = _l.lib().b200_w4a16_allreduce_oneshot(
-            ctypes.cast(self._in[i], ctypes.c_void_p), ctypes.cast(self._sig[i], ctypes.c_void_p),
-            _l._ptr(self.epoch[i]), _l._ptr(out), elems, _l.dtype_code(self.dtype), self.rank, self.world,
-            _l._stream(stream))
+        if two_shot is None:
+            # measured on 4 B200s (profiles/r01/f_allreduce_4gpu.txt): the second cross-GPU barrier of the
+            # two-shot form costs more than the bytes it saves up to [64, 8192] fp16 -> one-shot by default
+            two_shot = False
+        rc = _l.lib().b200_w4a16_allreduce(
+            ctypes.cast(self._in[i], ctypes.c_void_p), ctypes.cast(self._res[i], ctypes.c_void_p),
+            ctypes.cast(self._sig[i], ctypes.c_void_p), _l._ptr(self.epoch[i]), _l._ptr(out), elems,
+            _l.dtype_code(self.dtype), self.rank, self.world, 1 if two_shot else 0, _l._stream(stream))
         if rc:
             _l._raise(rc)
         self._turn ^= 1

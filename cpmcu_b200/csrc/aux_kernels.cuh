@@ -115,53 +115,92 @@ constexpr int kArMaxBlocks = 128;
 
 struct AllReduceArgs {
   const void* in[kArMaxWorld];  // every rank's symmetric input buffer (peer-mapped addresses)
-  int* sig[kArMaxWorld];        // every rank's signal pad: int[kArMaxBlocks][kArMaxWorld]
-  int* epoch;                   // local: int[kArMaxBlocks], calls completed per block
+  void* res[kArMaxWorld];       // two-shot only: every rank's symmetric result buffer
+  int* sig[kArMaxWorld];        // every rank's signal pad: int[2][kArMaxBlocks][kArMaxWorld]
+  int* epoch;                   // local: int[2][kArMaxBlocks], barriers completed per phase bank and block
   void* out;                    // local T[elems]
   long long elems;
   int rank, world;
 };
 
-template <typename T>
-__global__ void __launch_bounds__(256)
-allreduce_oneshot_kernel(const AllReduceArgs a) {
-  using T2 = typename Elem<T>::T2;
-  const int b = blockIdx.x;
-  const int target = a.epoch[b] + 1;
+// all peers' block b tell each other "phase reached" (fire-and-forget red.release.sys on the peer's
+// counter) and wait until every peer has said so; `phase` selects the counter bank
+__device__ __forceinline__ void ar_block_barrier(const AllReduceArgs& a, int b, int phase, int target) {
   if (threadIdx.x < a.world) {
     const int w = threadIdx.x;
-    asm volatile("red.release.sys.global.add.s32 [%0], 1;" ::"l"(a.sig[w] + b * kArMaxWorld + a.rank) : "memory");
-    const int* mine = a.sig[a.rank] + b * kArMaxWorld + w;
+    const int slot = (phase * kArMaxBlocks + b) * kArMaxWorld;
+    asm volatile("red.release.sys.global.add.s32 [%0], 1;" ::"l"(a.sig[w] + slot + a.rank) : "memory");
+    const int* mine = a.sig[a.rank] + slot + w;
     // bounded: a peer that never arrives (a rank died) must not hang this GPU — give up after ~1 s;
     // the sums are then wrong and the caller's collective error handling takes over
     for (long long spin = 0; ld_acquire_sys(mine) - target < 0 && spin < (1ll << 24); ++spin) {
     }
   }
   __syncthreads();
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * 8;
-  for (long long i = (static_cast<long long>(b) * blockDim.x + threadIdx.x) * 8; i < a.elems; i += stride) {
-    float acc[8];
+}
+
+// fp32 sum, in rank order, of the 8 elements at offset i of every rank's input
+template <typename T>
+__device__ __forceinline__ uint4 ar_sum8(const AllReduceArgs& a, long long i) {
+  using T2 = typename Elem<T>::T2;
+  float acc[8];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-    uint4 v[kArMaxWorld];
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+  uint4 v[kArMaxWorld];
 #pragma unroll
-    for (int w = 0; w < kArMaxWorld; ++w)
-      if (w < a.world) v[w] = ld_relaxed_sys_v4(reinterpret_cast<const T*>(a.in[w]) + i);
+  for (int w = 0; w < kArMaxWorld; ++w)
+    if (w < a.world) v[w] = ld_relaxed_sys_v4(reinterpret_cast<const T*>(a.in[w]) + i);
 #pragma unroll
-    for (int w = 0; w < kArMaxWorld; ++w)
-      if (w < a.world) {
-        const T2* h = reinterpret_cast<const T2*>(&v[w]);
+  for (int w = 0; w < kArMaxWorld; ++w)
+    if (w < a.world) {
+      const T2* h = reinterpret_cast<const T2*>(&v[w]);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          acc[2 * e] += Elem<T>::to_float(h[e].x);
-          acc[2 * e + 1] += Elem<T>::to_float(h[e].y);
-        }
+      for (int e = 0; e < 4; ++e) {
+        acc[2 * e] += Elem<T>::to_float(h[e].x);
+        acc[2 * e + 1] += Elem<T>::to_float(h[e].y);
       }
-    uint4 o;
-    T* oh = reinterpret_cast<T*>(&o);
+    }
+  uint4 o;
+  T* oh = reinterpret_cast<T*>(&o);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) oh[e] = Elem<T>::from_float(acc[e]);
-    *reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.out) + i) = o;
+  for (int e = 0; e < 8; ++e) oh[e] = Elem<T>::from_float(acc[e]);
+  return o;
+}
+
+// TWO_SHOT = false: every rank adds all W partials itself (one NVLink round trip; reads W x elems).
+// TWO_SHOT = true : rank r adds only slice r (reduce-scatter out of peer memory) into its symmetric
+//   result buffer, a second block-level barrier, then every rank copies the W result slices
+//   (all-gather out of peer memory): reads 2 x elems instead of W x elems — for the large messages
+//   (M = 64: 1 MB) at W >= 4, where the one-shot form is NVLink-bandwidth bound.
+// Block b of every rank owns the same part of every slice, so the barriers pair block b with block b.
+template <typename T, bool TWO_SHOT>
+__global__ void __launch_bounds__(256)
+allreduce_kernel(const AllReduceArgs a) {
+  const int b = blockIdx.x;
+  const int target = a.epoch[b] + 1;
+  ar_block_barrier(a, b, 0, target);
+  const long long tid8 = (static_cast<long long>(b) * blockDim.x + threadIdx.x) * 8;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * 8;
+  if (!TWO_SHOT) {
+    for (long long i = tid8; i < a.elems; i += stride)
+      *reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.out) + i) = ar_sum8<T>(a, i);
+  } else {
+    const long long slice = ((a.elems / 8 + a.world - 1) / a.world) * 8;  // elements per rank slice
+    const long long lo = slice * a.rank;
+    const long long hi = lo + slice < a.elems ? lo + slice : a.elems;
+    for (long long i = lo + tid8; i < hi; i += stride)
+      *reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.res[a.rank]) + i) = ar_sum8<T>(a, i);
+    __syncthreads();  // the release in the barrier below is cumulative over the block's result stores
+    const int target1 = a.epoch[kArMaxBlocks + b] + 1;  // the second bank only advances in two-shot calls
+    ar_block_barrier(a, b, 1, target1);
+    if (threadIdx.x == 0) a.epoch[kArMaxBlocks + b] = target1;
+    for (int w = 0; w < a.world; ++w) {
+      const long long wlo = slice * w;
+      const long long whi = wlo + slice < a.elems ? wlo + slice : a.elems;
+      for (long long i = wlo + tid8; i < whi; i += stride)
+        *reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.out) + i) =
+            ld_relaxed_sys_v4(reinterpret_cast<const T*>(a.res[w]) + i);
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) a.epoch[b] = target;

@@ -631,34 +631,53 @@ int b200_w4a16_repack_gptq(const int32_t* qweight_gptq, int32_t* qweight_marlin,
   return 0;
 }
 
-int b200_w4a16_allreduce_oneshot(const void* const* peer_in, int32_t* const* peer_sig, int32_t* epoch, void* out,
-                                 int64_t elems, int dtype, int rank, int world, void* stream) {
+int b200_w4a16_allreduce(const void* const* peer_in, void* const* peer_res, int32_t* const* peer_sig,
+                         int32_t* epoch, void* out, int64_t elems, int dtype, int rank, int world, int two_shot,
+                         void* stream) {
   if (world < 1 || world > kArMaxWorld || rank < 0 || rank >= world)
     return fail(B200_W4A16_EINVAL, "allreduce: world must be 1..%d and 0 <= rank < world (got %d, %d)", kArMaxWorld, world, rank);
   if (elems <= 0 || elems % 8) return fail(B200_W4A16_EINVAL, "allreduce: elems must be a positive multiple of 8, got %lld", (long long)elems);
   if (dtype != 0 && dtype != 1) return fail(B200_W4A16_EINVAL, "dtype must be 0 or 1");
-  if (!peer_in || !peer_sig || !epoch || !out) return fail(B200_W4A16_EINVAL, "allreduce: null pointer argument");
+  if (!peer_in || !peer_sig || !epoch || !out || (two_shot && !peer_res))
+    return fail(B200_W4A16_EINVAL, "allreduce: null pointer argument");
   AllReduceArgs a;
   std::memset(&a, 0, sizeof(a));
   for (int w = 0; w < world; ++w) {
     a.in[w] = peer_in[w];
     a.sig[w] = peer_sig[w];
-    if (!a.in[w] || !a.sig[w]) return fail(B200_W4A16_EINVAL, "allreduce: null peer pointer for rank %d", w);
+    a.res[w] = two_shot ? peer_res[w] : nullptr;
+    if (!a.in[w] || !a.sig[w] || (two_shot && !a.res[w]))
+      return fail(B200_W4A16_EINVAL, "allreduce: null peer pointer for rank %d", w);
   }
   a.epoch = epoch;
   a.out = out;
   a.elems = elems;
   a.rank = rank;
   a.world = world;
-  long long blocks = (elems / 8 + 255) / 256;
+  // one-shot: blocks over the whole message; two-shot: blocks over one rank slice (block b of every
+  // rank owns the same part of every slice)
+  const long long span = two_shot ? ((elems / 8 + world - 1) / world) : elems / 8;
+  long long blocks = (span + 255) / 256;
   if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  if (blocks < 1) blocks = 1;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (dtype == 0) allreduce_oneshot_kernel<__half><<<static_cast<int>(blocks), 256, 0, st>>>(a);
-  else allreduce_oneshot_kernel<__nv_bfloat16><<<static_cast<int>(blocks), 256, 0, st>>>(a);
+  const int nb = static_cast<int>(blocks);
+  if (dtype == 0) {
+    if (two_shot) allreduce_kernel<__half, true><<<nb, 256, 0, st>>>(a);
+    else allreduce_kernel<__half, false><<<nb, 256, 0, st>>>(a);
+  } else {
+    if (two_shot) allreduce_kernel<__nv_bfloat16, true><<<nb, 256, 0, st>>>(a);
+    else allreduce_kernel<__nv_bfloat16, false><<<nb, 256, 0, st>>>(a);
+  }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(B200_W4A16_ECUDA, "allreduce launch: %s", cudaGetErrorString(e));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   return 0;
+}
+
+int b200_w4a16_allreduce_oneshot(const void* const* peer_in, int32_t* const* peer_sig, int32_t* epoch, void* out,
+                                 int64_t elems, int dtype, int rank, int world, void* stream) {
+  return b200_w4a16_allreduce(peer_in, nullptr, peer_sig, epoch, out, elems, dtype, rank, world, 0, stream);
 }
 
 }  // extern "C"

@@ -105,13 +105,20 @@ int b200_w4a16_repack_gptq(const int32_t* qweight_gptq, int32_t* qweight_marlin,
  * the GEMM when the path is sharded (the reference has no multi-GPU code).
  *   peer_in[w]   HOST array of `world` device pointers: rank w's symmetric input buffer T[elems], mapped
  *                into this process (e.g. torch.distributed._symmetric_memory buffer_ptrs)
- *   peer_sig[w]  HOST array of `world` device pointers: rank w's signal pad, int32[128][8], zero-initialised
- *   epoch        local device int32[128], zero-initialised, private to this (buffer, signal pad) pair
+ *   peer_sig[w]  HOST array of `world` device pointers: rank w's signal pad, int32[2][128][8], zero-initialised
+ *   epoch        local device int32[2][128], zero-initialised, private to this (buffer, signal pad) pair
  *   out          local T[elems]; elems a multiple of 8
  * Every rank must call it the same number of times in the same order; callers alternate between two
  * (input buffer) sets so that no trailing barrier is needed.  Graph-capturable. */
 int b200_w4a16_allreduce_oneshot(const void* const* peer_in, int32_t* const* peer_sig, int32_t* epoch,
                                  void* out, int64_t elems, int dtype, int rank, int world, void* stream);
+/* Same collective with a choice of algorithm.  two_shot = 1: rank r adds only slice r of the message
+ * out of peer memory into its symmetric result buffer peer_res[r] (T[elems]), a second block-level
+ * barrier, then every rank copies the W result slices — 2 x elems read over NVLink instead of
+ * W x elems; for large messages (M = 64) at W >= 4.  Signal pads are int32[2][128][8] in both modes. */
+int b200_w4a16_allreduce(const void* const* peer_in, void* const* peer_res, int32_t* const* peer_sig,
+                         int32_t* epoch, void* out, int64_t elems, int dtype, int rank, int world,
+                         int two_shot, void* stream);
 
 /* Process-wide default for programmatic dependent launch on entry points that take no opts
  * (b200_w4a16_gemm, b200_w4a16_linear_forward): 1 = every GEMM launch carries the PDL attribute so

@@ -27,7 +27,7 @@ for m in (1, 16, 64):
         buf = ar.next_input(m, N)
         buf.copy_(x)
         out = torch.empty_like(x)
-        ar.reduce(buf, out, stream=s)
+        ar.reduce(buf, out, stream=s, two_shot=bool(rep & 1))
         s.synchronize()
         if rep == 0: print(f"[{rank}] first reduce m={m} done", flush=True)
         ref = x.clone()
@@ -47,13 +47,18 @@ for m in (1, 16, 64):
     def ours():
         for _ in range(32):
             buf = ar.next_input(m, N)
-            ar.reduce(buf, out, stream=s)
+            ar.reduce(buf, out, stream=s, two_shot=False)
+
+    def ours2():
+        for _ in range(32):
+            buf = ar.next_input(m, N)
+            ar.reduce(buf, out, stream=s, two_shot=True)
 
     def nccl():
         for _ in range(32):
             dist.all_reduce(x)
 
-    for name, fn in (("oneshot", ours), ("nccl", nccl)):
+    for name, fn in (("oneshot", ours), ("twoshot", ours2), ("nccl", nccl)):
         fn()
         s.synchronize()
         gr = torch.cuda.CUDAGraph()
