@@ -177,6 +177,11 @@ template <typename T, bool TWO_SHOT>
 __global__ void __launch_bounds__(256)
 allreduce_kernel(const AllReduceArgs a) {
   const int b = blockIdx.x;
+  // PDL: the next kernel in the stream (the following linear) may start its prologue and weight
+  // prefetch now; this kernel waits for the GEMM that produced its input before telling the peers
+  // "my partial is complete" (both are no-ops unless the launches carry the attribute)
+  pdl_launch_dependents();
+  pdl_wait_prior_grids();
   const int target = a.epoch[b] + 1;
   ar_block_barrier(a, b, 0, target);
   const long long tid8 = (static_cast<long long>(b) * blockDim.x + threadIdx.x) * 8;

@@ -662,13 +662,29 @@ int b200_w4a16_allreduce(const void* const* peer_in, void* const* peer_res, int3
   if (blocks < 1) blocks = 1;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int nb = static_cast<int>(blocks);
+  cudaLaunchConfig_t cfg;
+  std::memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(nb);
+  cfg.blockDim = dim3(256);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  // PDL on the collective is opt-in (B200_W4A16_AR_PDL=1): measured on 2 B200s it helps the tcgen05
+  // regime (M = 64: 2.55 -> 2.40 ms) but lets three kernels crowd each SM in the streaming regime
+  // (M = 1: 1.39 -> 1.89 ms), profiles/r01/README.md
+  static const bool ar_pdl = [] { const char* e = std::getenv("B200_W4A16_AR_PDL"); return e && e[0] == '1'; }();
+  cfg.numAttrs = (ar_pdl && g_default_pdl.load(std::memory_order_relaxed)) ? 1 : 0;
+  cudaError_t le;
   if (dtype == 0) {
-    if (two_shot) allreduce_kernel<__half, true><<<nb, 256, 0, st>>>(a);
-    else allreduce_kernel<__half, false><<<nb, 256, 0, st>>>(a);
+    le = two_shot ? cudaLaunchKernelEx(&cfg, allreduce_kernel<__half, true>, a)
+                  : cudaLaunchKernelEx(&cfg, allreduce_kernel<__half, false>, a);
   } else {
-    if (two_shot) allreduce_kernel<__nv_bfloat16, true><<<nb, 256, 0, st>>>(a);
-    else allreduce_kernel<__nv_bfloat16, false><<<nb, 256, 0, st>>>(a);
+    le = two_shot ? cudaLaunchKernelEx(&cfg, allreduce_kernel<__nv_bfloat16, true>, a)
+                  : cudaLaunchKernelEx(&cfg, allreduce_kernel<__nv_bfloat16, false>, a);
   }
+  if (le != cudaSuccess) return fail(B200_W4A16_ECUDA, "allreduce launch: %s", cudaGetErrorString(le));
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(B200_W4A16_ECUDA, "allreduce launch: %s", cudaGetErrorString(e));
   g_launches.fetch_add(1, std::memory_order_relaxed);
