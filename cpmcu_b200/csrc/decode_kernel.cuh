@@ -40,6 +40,7 @@ struct DecodeArgs {
   int ncols;      // column tiles = ceil(N / TN)
   int kblks;      // K / KB
   int slot_max;   // slots per column reserved in c_tmp
+  int colpar;     // 1: CTAs take whole columns (no split columns, no reduction through c_tmp)
   unsigned long long* dbg_ts;  // tuning only: per-CTA phase timestamps or null
 };
 
@@ -79,7 +80,7 @@ struct DecodeCfg {
   static constexpr int THREADS = WARPS * 32 + 64;  // + producer warp + flusher warp
   static constexpr int FLAGS_PER_TILE = CHUNKS * 16;  // ints of `workspace` owned by one column tile
   static_assert(WARPS % CHUNKS == 0 && KROWS % WK == 0, "warp layout");
-  static_assert(KB % 64 == 0 && (KB <= 128 || (KB == 256 && WK <= 8)), "stage k: a multiple of the 128-byte activation row; one group, or two whole groups");
+  static_assert(KB % 64 == 0 && (KB <= 128 || (KB % 128 == 0 && 8 % WK == 0)), "stage k: a multiple of the 128-byte activation row; one group, or whole groups whose 8 k16-rows fall to one row index i of every warp");
   static_assert(A_SUB % 1024 == 0 && W_STAGE % 1024 == 0, "TMA swizzle alignment");
 };
 
@@ -194,8 +195,11 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
 
   const long long units = static_cast<long long>(p.ncols) * p.kblks;
   const int grid = gridDim.x;
-  const int u0 = unit_begin(blockIdx.x, units, grid);
-  const int u1 = unit_begin(blockIdx.x + 1, units, grid);
+  // stream-K: an even split of the (column, k-block) units; column-parallel: an even split of whole columns
+  const int u0 = p.colpar ? static_cast<int>((static_cast<long long>(blockIdx.x) * p.ncols) / grid) * p.kblks
+                          : unit_begin(blockIdx.x, units, grid);
+  const int u1 = p.colpar ? static_cast<int>((static_cast<long long>(blockIdx.x + 1) * p.ncols) / grid) * p.kblks
+                          : unit_begin(blockIdx.x + 1, units, grid);
   const int my_units = u1 - u0;
   if (my_units == 0) return;
 
@@ -330,16 +334,21 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   for (int it = 0; it < my_units; ++it) {
     mbar_wait(bar_full + 8 * s, ph);
 
-    uint32_t s_lo[Cfg::SG][4], s_hi[Cfg::SG][4];
-    if (GROUPED) {
+    // scales of the stage's groups: held for the whole stage when there are at most two, else fetched as
+    // each warp's row index i enters a new group (fewer live registers)
+    constexpr bool LAZY_S = Cfg::SG > 2 && NT > 1;
+    constexpr int SGL = LAZY_S ? 1 : Cfg::SG;
+    uint32_t s_lo[SGL][4], s_hi[SGL][4];
+    auto load_scales = [&](int slot, int gi) {
+      const uint4 sv = lds128(sbase + Cfg::OFF_S + s * Cfg::S_STAGE + gi * (TN * 2) + s_off);
+      broadcast_scale_pair(sv.x, s_lo[slot][0], s_hi[slot][0]);
+      broadcast_scale_pair(sv.y, s_lo[slot][1], s_hi[slot][1]);
+      broadcast_scale_pair(sv.z, s_lo[slot][2], s_hi[slot][2]);
+      broadcast_scale_pair(sv.w, s_lo[slot][3], s_hi[slot][3]);
+    };
+    if (GROUPED && !LAZY_S) {
 #pragma unroll
-      for (int gi = 0; gi < Cfg::SG; ++gi) {
-        const uint4 sv = lds128(sbase + Cfg::OFF_S + s * Cfg::S_STAGE + gi * (TN * 2) + s_off);
-        broadcast_scale_pair(sv.x, s_lo[gi][0], s_hi[gi][0]);
-        broadcast_scale_pair(sv.y, s_lo[gi][1], s_hi[gi][1]);
-        broadcast_scale_pair(sv.z, s_lo[gi][2], s_hi[gi][2]);
-        broadcast_scale_pair(sv.w, s_lo[gi][3], s_hi[gi][3]);
-      }
+      for (int gi = 0; gi < Cfg::SG; ++gi) load_scales(gi, gi);
     }
     const uint32_t wst = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
     const uint32_t ast = sbase + Cfg::OFF_A + s * Cfg::A_STAGE;
@@ -361,11 +370,12 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
         for (int np = 0; np < NT / 2; ++np)  // token rows +16 per pair: 2048 B, swizzle phase unchanged
           ldmatrix_x4(bf[2 * np][0], bf[2 * np][1], bf[2 * np + 1][0], bf[2 * np + 1][1], a_row + np * 2048);
       }
+      if (GROUPED && LAZY_S && (RI & 7) == 0) load_scales(0, RI >> 3);
       const uint32_t qq[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         uint32_t w[4];
-        const int gi = Cfg::SG > 1 ? (RI >> 3) : 0;  // rows 8.. of a two-group stage use the second scale row
+        const int gi = (Cfg::SG > 1 && !LAZY_S) ? (RI >> 3) : 0;  // rows 8.. of a multi-group stage use the next scale rows
         Dequant<T>::template word<GROUPED>(qq[j], s_lo[gi][j], s_hi[gi][j], w);
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) mma_m16n8k16<T>(acc[j][nt], w, bf[nt][0], bf[nt][1]);

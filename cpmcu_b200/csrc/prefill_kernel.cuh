@@ -52,7 +52,7 @@ struct PrefillCfg {
   // dequant warps work in DGROUPS groups that take alternate k-blocks (group g: every k-block whose
   // running index has parity g), so a warp converts more k16-rows per barrier round trip
   static constexpr int DGROUPS =
-      ((DW / 2) >= CHUNKS && (DW / 2) % CHUNKS == 0 && STAGES % 2 == 0 && QSTAGES % 2 == 0) ? 2 : 1;
+      ((DW / 2) >= CHUNKS && (DW / 2) % CHUNKS == 0 && STAGES >= 2 && QSTAGES >= 2) ? 2 : 1;
   static constexpr int DWG = DW / DGROUPS;         // dequant warps per group = arrivals per stage
   static constexpr int WPC = DWG / CHUNKS;         // dequant warps of a group sharing a chunk
   static constexpr int RPW = 4 / WPC;              // k16-rows per dequant warp per stage
@@ -62,10 +62,10 @@ struct PrefillCfg {
   static constexpr int OFF_S = OFF_Q + QSTAGES * Q_STAGE;
   static constexpr int OFF_BAR = (OFF_S + QSTAGES * S_STAGE + 127) / 128 * 128;
   static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4;
-  static constexpr int SMEM_BYTES = OFF_BAR + NBARS * 8 + 16 + 1024;  // +1024: manual alignment
+  static constexpr int SMEM_BYTES = OFF_BAR + NBARS * 8 + 16;
   static constexpr int THREADS = (7 + DW) * 32;
   static_assert(DWG % CHUNKS == 0 && WPC >= 1 && 4 % WPC == 0, "dequant warp layout");
-  static_assert(DGROUPS == 1 || (STAGES % 2 == 0 && QSTAGES % 2 == 0), "two dequant groups walk the rings with stride 2");
+  static_assert(DGROUPS <= STAGES && DGROUPS <= QSTAGES, "the dequant groups walk the rings with stride DGROUPS (at most one wrap per step)");
   static_assert(TMEM_COLS >= 32 && TMEM_COLS <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "tensor memory allocation");
   static_assert(!SPLIT || (NSUB == 1 && RED_BYTES <= OFF_BAR), "split-K staging must fit in the dead rings (A, W and Q are all drained when the accumulator is complete)");
   static_assert(BM % 16 == 0 && BM <= 256, "UMMA N");
@@ -79,10 +79,12 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
   using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
   constexpr int CHUNKS = Cfg::CHUNKS;
 
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  // no static shared memory in this kernel: the dynamic window starts 1024-aligned (SWIZZLE_128B operand
+  // tiles need it); checked, not assumed
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
   const uint32_t sbase = smem_u32(smem);
+  if ((sbase & 1023u) != 0u) __trap();
   const uint32_t bar0 = sbase + Cfg::OFF_BAR;
   const uint32_t bar_a_full = bar0;
   const uint32_t bar_w_full = bar_a_full + STAGES * 8;

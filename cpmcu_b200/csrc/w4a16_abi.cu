@@ -8,6 +8,7 @@
 #include "../../include/b200_w4a16.h"
 
 #include <atomic>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -222,10 +223,18 @@ int launch_decode(const GemmCall& g) {
   }
   const long long slots = static_cast<long long>(sm_count()) * occ;
   int grid = static_cast<int>(units < slots ? units : slots);
-  // a column may be shared by at most 15 CTAs (16 ints of `workspace` per 64 columns: one flag per
-  // sharer + the completion counter)
-  while (grid > 1 && decode_slot_max(args.kblks, units, grid) > 15) --grid;
-  args.slot_max = decode_slot_max(args.kblks, units, grid);
+  // column-parallel geometry: CTAs take whole 64-column tiles (no split column, hence no cross-CTA
+  // reduction tail); some SMs idle when there are fewer tiles than SMs
+  args.colpar = (CHUNKS == 1 && KROWS >= 32) ? 1 : 0;
+  if (args.colpar) {
+    grid = static_cast<int>(args.ncols < slots ? args.ncols : slots);
+    args.slot_max = 1;
+  } else {
+    // a column may be shared by at most 15 CTAs (16 ints of `workspace` per 64 columns: one flag per
+    // sharer + the completion counter)
+    while (grid > 1 && decode_slot_max(args.kblks, units, grid) > 15) --grid;
+    args.slot_max = decode_slot_max(args.kblks, units, grid);
+  }
   args.dbg_ts = stream_debug_next_slot();
 
   cudaLaunchConfig_t cfg;
@@ -253,8 +262,10 @@ int launch_decode(const GemmCall& g) {
 #define DECODE_FAMILY(T, DT, NT, GR)                                                    \
   DCFG(T, DT, NT, 2, 8, 8, 8, GR), DCFG(T, DT, NT, 4, 8, 8, 5, GR), DCFG(T, DT, NT, 4, 4, 8, 8, GR), \
       DCFG(T, DT, NT, 8, 4, 8, 5, GR), DCFG(T, DT, NT, 4, 8, 16, 5, GR), DCFG(T, DT, NT, 2, 8, 16, 8, GR), \
-      DCFG(T, DT, NT, 2, 16, 8, 5, GR), DCFG(T, DT, NT, 1, 16, 4, 8, GR), DCFG(T, DT, NT, 3, 16, 12, 3, GR)
-constexpr int kGeoms = 9;
+      DCFG(T, DT, NT, 2, 16, 8, 5, GR), DCFG(T, DT, NT, 1, 16, 4, 8, GR), DCFG(T, DT, NT, 3, 16, 12, 3, GR), \
+      DCFG(T, DT, NT, 1, 32, 8, 4, GR)
+constexpr int kGeoms = 10;
+constexpr int kColparGeom = 9;  // 64-column x 512-k stages, launched column-parallel (see launch_decode)
 
 const DecodeConfig g_decode[] = {
     DECODE_FAMILY(__half, 0, 1, true),          DECODE_FAMILY(__half, 0, 2, true),
@@ -277,8 +288,19 @@ int nt_for_m(int m) { return m <= 8 ? 1 : (m <= 16 ? 2 : 4); }
 // x 128-k stage with 8 consumer warps (4 k16-rows per warp and stage) has the fewest instructions per
 // byte and leaves room for the next kernel's CTA on the same SM (PDL); stream-K balances any shape.
 int pick_geometry(int m, int n, int k) {
-  (void)m;
-  (void)n;
+  // column-parallel (no split column) against stream-K: an SM streams about 29 bytes/ns of int4 at
+  // M <= 8 (24 at M <= 16, 17 beyond; in-loop rates of profiles/r01 g_timeline); stream-K keeps every SM
+  // busy but ends in the cross-CTA reduction of the split columns (about 3.5 us at M <= 8, 5 us beyond)
+  static const int colpar_mode = [] { const char* e = std::getenv("B200_W4A16_COLPAR"); return e ? std::atoi(e) : 0; }();
+  if ((k % 512) == 0 && colpar_mode != 0) {
+    const double rate = m <= 8 ? 29e3 : (m <= 16 ? 24e3 : 17e3);  // bytes per us and SM
+    const double tail = m <= 8 ? 3.5 : 5.0;
+    const double col_bytes = 32.0 * k, cols = n / 64.0;
+    const int sms = sm_count();
+    const double t_colpar = std::ceil(cols / sms) * col_bytes / rate;
+    const double t_streamk = cols * col_bytes / (rate * sms) + tail;
+    if (colpar_mode == 1 || t_colpar < t_streamk) return kColparGeom;
+  }
   return (k % 128) == 0 ? 1 : 2;  // tn256/kb128/w8, or tn256/kb64/w8 when K is only a multiple of 64
 }
 
@@ -314,7 +336,7 @@ void prefill_from_id(int id, int* tile, int* S) {
 }
 
 struct Geom { int chunks, krows; };
-const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}, {2, 16}, {1, 16}, {3, 16}};
+const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}, {2, 16}, {1, 16}, {3, 16}, {1, 32}};
 
 }  // namespace b200
 

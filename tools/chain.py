@@ -21,6 +21,7 @@ ap.add_argument("--layers", type=int, default=32)
 ap.add_argument("--combo", action="append", default=[])
 ap.add_argument("--no-pdl", action="store_true")
 ap.add_argument("--reps", type=int, default=10)
+ap.add_argument("--only", default="", help="chain only this shape (qkv|o|gate_up|down)")
 args = ap.parse_args()
 dev = "cuda"
 m = args.m
@@ -43,6 +44,8 @@ def resolve(x):
 lay = []
 for li in range(args.layers):
     for nm, k, n in SHAPES:
+        if args.only and nm != args.only:
+            continue
         qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=dev)
         sc = (torch.rand((k // 128, n), device=dev) * 0.018 + 0.002).half()
         lay.append((nm, k, n, qw, sc))
