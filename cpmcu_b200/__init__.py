@@ -5,7 +5,8 @@ src/qgemm/gptq_marlin) rebuilt as hand-written sm_100a CUDA behind a C ABI (incl
 The package holds only what that path needs:
   csrc/            CUDA kernels + the C ABI            -> libb200_w4a16.so (built in-tree)
   capi.py          ctypes binding of the C ABI (fails loudly when the library is missing)
-  linear.py        W4A16GPTQMarlinLinear: host-side mirror of the reference operator
+  linear.py        W4A16GPTQMarlinLinear (+ the un-quantised Linear / LMHead of the same model at decode
+                   widths): host-side mirrors of the reference operators
 """
 from .capi import (  # noqa: F401
     B200W4A16Error,
@@ -13,6 +14,7 @@ from .capi import (  # noqa: F401
     BF16,
     gemm,
     dequant,
+    dense_linear,
     lib,
     library_path,
     reduce_bytes,
@@ -21,4 +23,4 @@ from .capi import (  # noqa: F401
     launch_count,
     set_pdl,
 )
-from .linear import W4A16GPTQMarlinLinear  # noqa: F401
+from .linear import W4A16GPTQMarlinLinear, Linear, LMHead  # noqa: F401

@@ -50,6 +50,8 @@ SYMBOLS = {
     "b200_w4a16_linear_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_int, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p,
                                           c_void_p]),
+    "b200_w4a16_dense_linear_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64,
+                                                c_int64, c_float, c_int, c_int, c_void_p]),
     "b200_w4a16_dequant": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p]),
     "b200_w4a16_repack_gptq": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "b200_w4a16_reduce_max_m": (c_int, [c_int64]),
@@ -166,6 +168,29 @@ def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm
                                   _ptr(out), m, n, k, group_size, dtype_code(a.dtype), 1,
                                   0 if perm is None else 1, _ptr(a_tmp), _ptr(c_tmp), _stream(stream),
                                   ctypes.byref(o))
+    if rc:
+        _raise(rc)
+    return out
+
+
+def dense_linear(a, weight, out=None, *, bias=None, inplace=False, input_scale=1.0, pdl=False, stream=None):
+    """out[M,N] = (a * T(input_scale)) @ weight.T (+ out when inplace) (+ bias): the un-quantised lm_head /
+    draft-head linear at M <= 64, one HBM-streaming launch (reference: src/model/linear.cuh:8-37,76-105).
+
+    a: [M,K] fp16/bf16 cuda, weight: [N,K] same dtype (nn.Linear layout)."""
+    import torch
+    assert a.is_cuda and a.is_contiguous() and weight.is_contiguous() and a.dtype == weight.dtype
+    m, k = a.shape
+    n = weight.shape[0]
+    if weight.shape[1] != k:
+        raise ValueError(f"dense_linear: weight is {tuple(weight.shape)}, input has K = {k}")
+    if out is None:
+        if inplace:
+            raise ValueError("dense_linear: inplace needs `out`")
+        out = torch.empty((m, n), dtype=a.dtype, device=a.device)
+    rc = lib().b200_w4a16_dense_linear_forward(_ptr(a), _ptr(weight), _ptr(bias), _ptr(out), 1 if inplace else 0,
+                                               m, n, k, float(input_scale), dtype_code(a.dtype), 1 if pdl else 0,
+                                               _stream(stream))
     if rc:
         _raise(rc)
     return out

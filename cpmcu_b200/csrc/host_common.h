@@ -29,6 +29,7 @@ struct GemmCall {
 int fail(int code, const char* fmt, ...);
 int sm_count();
 extern std::atomic<long long> g_launches;
+extern std::atomic<int> g_default_pdl;  // b200_w4a16_set_pdl
 // rank 2 or 3 tiled TMA descriptor (cached); dims/strides innermost first (strides[] in bytes for dims 1..)
 int get_tensor_map(CUtensorMap* out, const void* ptr, CUtensorMapDataType type, int rank,
                    const uint64_t* dims, const uint64_t* strides, const uint32_t* box,

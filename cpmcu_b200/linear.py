@@ -81,3 +81,75 @@ class W4A16GPTQMarlinLinear:
         return tgt if tgt is not None else out
 
     decode = prefill  # the reference's decode paths call prefill() (w4a16_gptq_marlin_ffn.cuh:67-78)
+
+
+class Linear:
+    """Host-side mirror of the reference's un-quantised `Linear<T>` (src/model/linear.cuh:39-85) for the
+    decode / tree-verify widths (num_tokens <= 64): weight T[dim_out][dim_in] (`transposed=True`, the only
+    layout CPM.cu instantiates), optional bias, same method names and argument meaning.  The GEMM, the
+    inplace add and the bias add are ONE weight-streaming launch through the C ABI."""
+
+    def __init__(self, dim_in: int, dim_out: int, transposed: bool = True, has_bias: bool = False,
+                 dtype=None, device="cuda"):
+        import torch
+        if not transposed:
+            raise ValueError("Linear: only transposed=True (weight [dim_out][dim_in]) is supported")
+        self.dim_in, self.dim_out = dim_in, dim_out
+        self.transposed, self.has_bias = transposed, has_bias
+        self.dtype = torch.float16 if dtype is None else dtype
+        self.device = torch.device(device)
+        self.weight = self.bias = self.output = None
+        self.input_scale = 1.0
+
+    def init_weight_ptr(self, memory=None):
+        import torch
+        self.weight = torch.empty((self.dim_out, self.dim_in), dtype=self.dtype, device=self.device)
+        if self.has_bias:
+            self.bias = torch.empty((self.dim_out,), dtype=self.dtype, device=self.device)
+
+    def init_output_ptr(self, memory, num_tokens: int, offset: int = 0) -> int:
+        import torch
+        self.output = torch.empty((num_tokens, self.dim_out), dtype=self.dtype, device=self.device)
+        return offset + num_tokens * self.dim_out * self.output.element_size()
+
+    def load_to_storage(self, name: str, tensor):
+        """name routing of src/model/linear.cuh:65-73 ("weight" / "bias")."""
+        import torch
+        if self.weight is None:
+            self.init_weight_ptr()
+        t = tensor if isinstance(tensor, torch.Tensor) else torch.as_tensor(tensor)
+        if "weight" in name:
+            self.weight.copy_(t.reshape(self.weight.shape).to(self.dtype), non_blocking=True)
+        elif "bias" in name:
+            if self.bias is None:
+                raise ValueError("Unsupported name " + name)
+            self.bias.copy_(t.reshape(self.bias.shape).to(self.dtype), non_blocking=True)
+        else:
+            raise ValueError("Unsupported name " + name)
+
+    def prefill(self, stream, num_tokens: int, input, tgt=None, inplace: bool = False):
+        """src/model/linear.cuh:76-82: result in self.output (tgt None) or tgt; inplace: tgt += result."""
+        if tgt is None:
+            if self.output is None:
+                self.init_output_ptr(None, num_tokens)
+            tgt = self.output[:num_tokens]
+        rc = _l.lib().b200_w4a16_dense_linear_forward(
+            _l._ptr(input), _l._ptr(self.weight), _l._ptr(self.bias) if self.has_bias else None, _l._ptr(tgt),
+            1 if inplace else 0, num_tokens, self.dim_out, self.dim_in, float(self.input_scale),
+            _l.dtype_code(self.dtype), -1, _l._stream(stream))
+        if rc:
+            _l._raise(rc)
+        return tgt
+
+    decode = prefill
+
+
+class LMHead(Linear):
+    """`LMHead<T>` (src/model/linear.cuh:86-105): the input is scaled by T(head_scale) (rounded to T, as
+    elementwise_scale does) before the linear — fused into the same launch, no tmp_hidden_size buffer."""
+
+    def __init__(self, dim_in: int, dim_out: int, head_scale: float = 1.0, transposed: bool = True,
+                 has_bias: bool = False, dtype=None, device="cuda"):
+        super().__init__(dim_in, dim_out, transposed, has_bias, dtype, device)
+        self.head_scale = head_scale
+        self.input_scale = head_scale

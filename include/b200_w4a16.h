@@ -100,6 +100,24 @@ int b200_w4a16_dequant(const int32_t* qweight, const void* scales, void* w_out, 
 int b200_w4a16_repack_gptq(const int32_t* qweight_gptq, int32_t* qweight_marlin, int64_t n, int64_t k,
                            void* stream);
 
+/* Un-quantised fp16 / bf16 linear at decode / tree-verify widths: out[M][N] = (input * T(input_scale)) . weight^T.
+ * Replaces linear<T>() = cublasGemmEx(OP_T, OP_N, CUBLAS_COMPUTE_32F) as called by Linear<T>::prefill and
+ * LMHead<T>::prefill (src/model/linear.cuh:8-37,76-105) for `transposed = true` weights — the lm_head
+ * (73448 x 4096, 602 MB read per verify step), the FR-Spec / EAGLE draft heads and EAGLE fc1 / fc2
+ * (src/model/eagle.cuh:301-302,446,470) — with one HBM-streaming launch (no cuBLAS, no staging buffer).
+ *   weight       T[N][K] row-major (torch nn.Linear layout), 16-byte aligned; K % 8 == 0
+ *   input        T[M][K], M <= 64 (the reference sizes the lm_head output for 64 tokens, src/model/model.cuh:116);
+ *                larger M is a value error: that regime is a library GEMM, not a weight stream
+ *   input_scale  LMHead::head_scale: the input is multiplied by T(input_scale) and rounded to T first
+ *                (elementwise_scale, src/model/elementwise.cuh:35-41); 1.0f = plain Linear
+ *   inplace      out = RN_T(out + gemm)  (cuBLAS beta = 1: one rounding), else out = RN_T(gemm)
+ *   bias         T[N] or NULL, added afterwards in T (batched_add, src/model/elementwise.cuh:8-14)
+ *   pdl          1 / 0 = launch with / without programmatic dependent launch; -1 = the process default
+ *                (b200_w4a16_set_pdl) */
+int b200_w4a16_dense_linear_forward(const void* input, const void* weight, const void* bias, void* output,
+                                    int inplace, int64_t num_tokens, int64_t dim_out, int64_t dim_in,
+                                    float input_scale, int dtype, int pdl, void* stream);
+
 /* One-shot all-reduce (sum, in rank order, fp32 accumulate) of the [M][N] partial outputs of a
  * row-parallel linear (o / down sharded along K) over NVLink peer memory — the collective that follows
  * the GEMM when the path is sharded (the reference has no multi-GPU code).

@@ -237,6 +237,32 @@ def linear_forward(a, qweight, scales_marlin, size_k, size_n, group_size=128, dt
     return to_storage(res, dtype)
 
 
+def dense_linear(a, weight, dtype=FP16, bias=None, tgt=None, inplace=False, head_scale=1.0):
+    """Un-quantised Linear<T>::prefill / LMHead<T>::prefill (src/model/linear.cuh:8-37,76-105) restated:
+      LMHead: input * T(head_scale), rounded to T (elementwise_scale_kernel, elementwise.cuh:35-41);
+      cublasGemmEx(OP_T, OP_N, CUBLAS_COMPUTE_32F): out = RN_T(sum_k a[m,k] w[n,k] + beta * out), beta = 1
+      when inplace (one rounding); has_bias: out = RN_T(out + bias) (batched_add, elementwise.cuh:8-14).
+    weight is [N][K] (`transposed = true`).  The sum is taken in fp64 (order-free truth; cuBLAS and the
+    CUDA kernel accumulate in fp32 in their own orders).  Returns (out in storage dtype, out before the
+    roundings of the GEMM result as real numbers)."""
+    a32 = to_f32(np.asarray(a), dtype)
+    if head_scale != 1.0:
+        sv = to_f32(to_storage(np.array([head_scale], dtype=np.float32), dtype), dtype)[0]
+        a32 = to_f32(to_storage(a32 * sv, dtype), dtype)   # fp32 product of two T values is exact -> one RN
+    w32 = to_f32(np.asarray(weight), dtype)
+    acc = a32.astype(np.float64) @ w32.astype(np.float64).T
+    if inplace:
+        assert tgt is not None
+        acc = acc + to_f32(np.asarray(tgt), dtype).astype(np.float64)
+    exact = acc
+    res = to_f32(to_storage(acc, dtype), dtype)
+    if bias is not None:
+        b = to_f32(np.asarray(bias), dtype)[None, :]
+        exact = exact + b
+        res = to_f32(to_storage(res + b, dtype), dtype)
+    return to_storage(res, dtype), exact
+
+
 def determine_reduce_max_m(prob_m: int, max_par: int = 16) -> int:
     """gptq_marlin_utils.cu:206-225"""
     for i in (1, 2, 3, 4):
