@@ -32,13 +32,14 @@ struct DenseArgs {
   uint32_t scale2;     // T(head_scale) twice (used when SCALED)
 };
 
-template <typename T, int NT, int TR, int STAGES>
+template <typename T, int NT, int TR, int KBLK, int STAGES>
 struct DenseCfg {
   static constexpr int WARPS = 8;
-  static constexpr int KB = 128;               // k per stage
+  static constexpr int KB = KBLK;              // k per stage
   static constexpr int KC = KB / 64;           // 128-byte sub-tiles per stage
   static constexpr int MTILES = TR / 16;       // 16-row MMA tiles of W per stage
-  static constexpr int WK = WARPS / MTILES;    // warps sharing a row tile (split over k16 steps)
+  static constexpr int MPW = MTILES >= WARPS ? MTILES / WARPS : 1;  // 16-row tiles per warp
+  static constexpr int WK = MTILES >= WARPS ? 1 : WARPS / MTILES;   // warps sharing a row tile (split over k16 steps)
   static constexpr int KS = KB / 16 / WK;      // k16 steps per warp and stage
   static constexpr int MT = NT * 8;            // token rows held in smem / accumulators
   static constexpr int W_SUB = TR * 128;
@@ -55,7 +56,8 @@ struct DenseCfg {
   static constexpr int OFF_BAR = OFF_RED + (RED_BYTES + 15) / 16 * 16;
   static constexpr int SMEM_BYTES = OFF_BAR + 2 * NS * 8 + 16;
   static constexpr int THREADS = WARPS * 32 + 32;  // + producer warp
-  static_assert(WARPS % MTILES == 0 && (KB / 16) % WK == 0, "warp layout");
+  static_assert((MTILES >= WARPS ? MTILES % WARPS == 0 : WARPS % MTILES == 0) && (KB / 16) % WK == 0 && KB % 64 == 0,
+                "warp layout");
   static_assert(W_SUB % 1024 == 0 && A_SUB % 1024 == 0, "TMA swizzle alignment");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory");
 };
@@ -74,12 +76,13 @@ __device__ __forceinline__ uint32_t mul2<__nv_bfloat16>(uint32_t a, uint32_t b) 
   return *reinterpret_cast<const uint32_t*>(&r);
 }
 
-template <typename T, int NT, int TR, int STAGES, bool SCALED>
-__global__ void __launch_bounds__(DenseCfg<T, NT, TR, STAGES>::THREADS, 1)
+template <typename T, int NT, int TR, int KBLK, int STAGES, bool SCALED>
+__global__ void __launch_bounds__(DenseCfg<T, NT, TR, KBLK, STAGES>::THREADS, 1)
 dense_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_a,
                     const DenseArgs p) {
-  using Cfg = DenseCfg<T, NT, TR, STAGES>;
+  using Cfg = DenseCfg<T, NT, TR, KBLK, STAGES>;
   constexpr int NS = Cfg::NS, KC = Cfg::KC, KB = Cfg::KB, WK = Cfg::WK, KS = Cfg::KS, TRP = Cfg::TRP;
+  constexpr int MPW = Cfg::MPW;
   constexpr int NCONS = Cfg::WARPS * 32;
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -159,15 +162,17 @@ dense_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   }
 
   // ======================================= consumers =======================================
-  const int wm = warp % Cfg::MTILES;  // 16-row tile of W inside the stage
-  const int wk = warp / Cfg::MTILES;  // k-slice: k16 steps wk*KS .. wk*KS + KS - 1
+  const int wm = (WK == 1) ? warp * MPW : warp % Cfg::MTILES;  // first 16-row tile of W of this warp
+  const int wk = (WK == 1) ? 0 : warp / Cfg::MTILES;           // k-slice: k16 steps wk*KS .. wk*KS + KS - 1
   const int g = lane >> 2, t = lane & 3;
 
-  float acc[NT][4];
+  float acc[MPW][NT][4];
 #pragma unroll
-  for (int nt = 0; nt < NT; ++nt)
+  for (int mp = 0; mp < MPW; ++mp)
 #pragma unroll
-    for (int e = 0; e < 4; ++e) acc[nt][e] = 0.f;
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[mp][nt][e] = 0.f;
 
   // ldmatrix row addresses inside the 128B-swizzled sub-tiles (16-byte chunk c of row r sits at
   // r*128 + ((c ^ (r & 7)) << 4)); k16 step ks covers chunks 2*(ks & 3), +1 of sub-tile ks >> 2.
@@ -192,9 +197,11 @@ dense_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
     for (int i = 0; i < KS; ++i) {
       const int ks = wk * KS + i;       // k16 step inside the stage (wk is warp-uniform)
       const int sub = ks >> 2, c0 = (ks & 3) * 2;
-      uint32_t wf[4];
-      ldmatrix_x4(wf[0], wf[1], wf[2], wf[3],
-                  wst + sub * Cfg::W_SUB + w_row * 128 + (((c0 + w_hi) ^ (w_row & 7)) << 4));
+      uint32_t wf[MPW][4];
+#pragma unroll
+      for (int mp = 0; mp < MPW; ++mp)  // +16 rows per tile: 2048 B, swizzle phase unchanged
+        ldmatrix_x4(wf[mp][0], wf[mp][1], wf[mp][2], wf[mp][3],
+                    wst + sub * Cfg::W_SUB + w_row * 128 + (((c0 + w_hi) ^ (w_row & 7)) << 4) + mp * 2048);
       uint32_t bf[NT][2];
       const uint32_t a_addr = ast + sub * Cfg::A_SUB + a_row * 128 + (((c0 + a_hi) ^ (a_row & 7)) << 4);
       if (NT == 1) {
@@ -210,7 +217,8 @@ dense_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
           bf[nt][0] = mul2<T>(bf[nt][0], p.scale2);
           bf[nt][1] = mul2<T>(bf[nt][1], p.scale2);
         }
-        mma_m16n8k16<T>(acc[nt], wf, bf[nt][0], bf[nt][1]);
+#pragma unroll
+        for (int mp = 0; mp < MPW; ++mp) mma_m16n8k16<T>(acc[mp][nt], wf[mp], bf[nt][0], bf[nt][1]);
       }
     }
     __syncwarp();
@@ -224,15 +232,17 @@ dense_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       for (int r = 0; r < WK; ++r) {
         if (wk == r) {
 #pragma unroll
-          for (int nt = 0; nt < NT; ++nt)
+          for (int mp = 0; mp < MPW; ++mp)
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int n = wm * 16 + g + ((e & 2) ? 8 : 0);
-              const int tok = nt * 8 + 2 * t + (e & 1);
-              float* dst = red + tok * TRP + n;
-              *dst = (r == 0) ? acc[nt][e] : (*dst + acc[nt][e]);
-              acc[nt][e] = 0.f;
-            }
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const int n = (wm + mp) * 16 + g + ((e & 2) ? 8 : 0);
+                const int tok = nt * 8 + 2 * t + (e & 1);
+                float* dst = red + tok * TRP + n;
+                *dst = (r == 0) ? acc[mp][nt][e] : (*dst + acc[mp][nt][e]);
+                acc[mp][nt][e] = 0.f;
+              }
         }
         named_bar_sync(1, NCONS);
       }

@@ -42,10 +42,10 @@ uint32_t scale_pair<__nv_bfloat16>(float v) {
   return static_cast<uint32_t>(u) | (static_cast<uint32_t>(u) << 16);
 }
 
-template <typename T, int NT, int TR, int STAGES, bool SCALED>
+template <typename T, int NT, int TR, int KBLK, int STAGES, bool SCALED>
 int launch_dense(const DenseCall& g) {
-  using Cfg = DenseCfg<T, NT, TR, STAGES>;
-  auto kern = dense_stream_kernel<T, NT, TR, STAGES, SCALED>;
+  using Cfg = DenseCfg<T, NT, TR, KBLK, STAGES>;
+  auto kern = dense_stream_kernel<T, NT, TR, KBLK, STAGES, SCALED>;
   static bool attr_set = false;  // benign race: idempotent
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -100,12 +100,12 @@ int launch_dense(const DenseCall& g) {
 
 template <typename T, bool SCALED>
 int dispatch_nt(const DenseCall& g) {
-  // 64-row tiles while the token block is small; 128-row tiles beyond, so that the activation boxes
-  // re-read from L2 per stage stay at most half the bytes of the weight boxes
-  if (g.m <= 8) return launch_dense<T, 1, 64, 8, SCALED>(g);
-  if (g.m <= 16) return launch_dense<T, 2, 64, 8, SCALED>(g);
-  if (g.m <= 32) return launch_dense<T, 4, 128, 4, SCALED>(g);
-  return launch_dense<T, 8, 128, 4, SCALED>(g);
+  // 64-row tiles while the token block is small; 128 / 256-row tiles beyond, so that the activation boxes
+  // re-read from L2 every stage stay at most a quarter of the bytes of the weight boxes
+  if (g.m <= 8) return launch_dense<T, 1, 64, 128, 8, SCALED>(g);
+  if (g.m <= 16) return launch_dense<T, 2, 64, 128, 8, SCALED>(g);
+  if (g.m <= 32) return launch_dense<T, 4, 128, 128, 4, SCALED>(g);
+  return launch_dense<T, 8, 256, 64, 4, SCALED>(g);
 }
 
 }  // namespace
