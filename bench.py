@@ -209,6 +209,7 @@ def main():
     ap.add_argument("--no-pdl", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-detail", action="store_true")
+    ap.add_argument("--no-lm-head", action="store_true", help="skip the un-quantised lm_head leg (SURVEY 8f-2)")
     ap.add_argument("--workload", default="auto", choices=["auto", "minicpm4", "llama70b"],
                     help="auto: MiniCPM4-8B linears at N=1, tensor-parallel Llama-3-70B linears at N>1")
     ap.add_argument("--collective", default="oneshot", choices=["oneshot", "nccl"],
@@ -414,9 +415,60 @@ def main():
     if use_ref_kernel:
         line["impl"] = "reference"
         line["roofline"]["note"] += "; this is the reference's kernel, reported for comparison"
+    if not args.no_lm_head:
+        line["lm_head"] = lm_head_leg(torch, dev, stream, widths, pk, ours=not use_ref_kernel)
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(torch, [q[0] for q in qw], [s[0] for s in sc], SHAPES_8B, 16)
     print(json.dumps(line), flush=True)
+
+
+def lm_head_leg(torch, dev, stream, widths, pk, ours, reps=16, iters=5):
+    """SURVEY.md section 8(f)-2, reported beside the headline metric (not part of `value`): the un-quantised
+    lm_head (73448 x 4096 fp16 = 602 MB > L2, streamed from HBM every launch) at the same widths — this
+    library's streaming kernel (ours) or cuBLAS via torch.matmul, which is what the reference's linear<T>()
+    calls (src/model/linear.cuh:8-37)."""
+    import cpmcu_b200 as B
+    n, k = 73448, 4096
+    g = torch.Generator(device=dev).manual_seed(7)
+    w = (torch.randn((n, k), generator=g, device=dev, dtype=torch.float32) * 0.02).half()
+    res = {}
+    for m in widths:
+        if m > 64:
+            continue
+        a = torch.randn((m, k), generator=g, device=dev, dtype=torch.float32).half()
+        out = torch.empty((m, n), dtype=torch.float16, device=dev)
+
+        def chain():
+            for _ in range(reps):
+                if ours:
+                    B.dense_linear(a, w, out, pdl=True, stream=stream)
+                else:
+                    torch.matmul(a, w.t(), out=out)
+        chain()
+        stream.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=stream):
+            chain()
+        for _ in range(3):
+            gr.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        best = 1e30
+        for _ in range(iters):
+            e0.record(stream)
+            gr.replay()
+            e1.record(stream)
+            stream.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        us = best / reps * 1e3
+        gbs = n * k * 2 / us / 1e3
+        res[str(m)] = dict(us=round(us, 2), gbs=round(gbs, 1), hbm_frac=round(gbs / pk["hbm"], 4),
+                           hbm_frac_nominal_8000=round(gbs / 8000.0, 4))
+        del gr
+    return {"workload": "un-quantised lm_head 73448x4096 fp16, weight bytes / device time, back-to-back launches "
+                        "in one CUDA graph" + (", PDL on" if ours else ""),
+            "kernel": "dense_stream_kernel (b200_w4a16_dense_linear_forward)" if ours else "cuBLAS via torch.matmul",
+            "note": "peak = the copy (read+write) bandwidth of MEASURED_PEAKS.json; a read-only stream can exceed it",
+            "per_width": res}
 
 
 def reference_cpu_arm(args, torch, dev, widths):
