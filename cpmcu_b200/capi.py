@@ -29,7 +29,8 @@ class Opts(ctypes.Structure):
         ("c_tmp_bytes", c_int64),
         ("force_config", c_int),
         ("pdl", c_int),
-        ("reserved", c_int * 5),
+        ("out_scale", c_float),
+        ("reserved", c_int * 4),
     ]
 
 
@@ -146,8 +147,8 @@ def config_name(cfg: int) -> str:
 
 
 def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm=None, a_tmp=None,
-         bias=None, residual=None, force_config=0, pdl=False, stream=None):
-    """C[M,N] = A[M,K] . dequant(qweight, scales)  (+ residual, + bias) on the current stream.
+         bias=None, residual=None, out_scale=0.0, force_config=0, pdl=False, stream=None):
+    """C[M,N] = A[M,K] . dequant(qweight, scales)  (+ residual, + bias, * T(out_scale)) on the current stream.
 
     a: [M,K] fp16/bf16 cuda, qweight: int32 [K/16, 2N] cuda (Marlin), scales: [K/g, N] (Marlin-permuted),
     workspace: int32 [(N/64)*16] zeroed, c_tmp: float32 scratch of >= reduce_bytes(M,N,K) bytes
@@ -162,6 +163,7 @@ def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm
     o.bias = None if bias is None else bias.data_ptr()
     o.residual = None if residual is None else residual.data_ptr()
     o.c_tmp_bytes = 0 if c_tmp is None else c_tmp.numel() * c_tmp.element_size()
+    o.out_scale = float(out_scale)
     o.force_config = force_config
     o.pdl = 1 if pdl else 0
     rc = lib().b200_w4a16_gemm_ex(_ptr(a), _ptr(qweight), _ptr(scales), None, _ptr(perm), _ptr(workspace),

@@ -266,6 +266,17 @@ struct Elem<__nv_bfloat16> {
   }
 };
 
+// last post-op of the epilogues: out = RN_T(out * T(scale)) (the layer's residual scaling, reference:
+// elementwise_scale, src/model/elementwise.cuh:35-41); os = 0: none, else 0x10000 | bits of T(scale)
+template <typename T>
+__device__ __forceinline__ T apply_out_scale(T o, uint32_t os) {
+  if (os) {
+    const uint16_t b = static_cast<uint16_t>(os & 0xffffu);
+    o = __hmul(o, *reinterpret_cast<const T*>(&b));
+  }
+  return o;
+}
+
 // D(16x8,f32) += A(16x16,T,row) * B(16x8,T,col): the register-operand tensor path.  In the
 // HBM-bound regime the weights arrive as registers straight out of the dequantiser, which is the
 // one case where mma.sync (not tcgen05, whose operands live in shared/tensor memory) is the right

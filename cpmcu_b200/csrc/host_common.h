@@ -18,6 +18,7 @@ struct GemmCall {
   float* c_tmp;
   const void* bias;
   const void* residual;
+  float out_scale;  // 0 = none
   int m, n, k;
   int group_size;
   int dtype;
@@ -26,6 +27,7 @@ struct GemmCall {
 };
 
 // defined in w4a16_abi.cu
+uint32_t out_scale_bits(float s, int dtype);  // 0 = none, else 0x10000 | bits of T(s)
 int fail(int code, const char* fmt, ...);
 int sm_count();
 extern std::atomic<long long> g_launches;

@@ -28,6 +28,7 @@ struct PrefillArgs {
   const void* scales;    // raw pointer (channelwise epilogue)
   const void* bias;      // T[N] or null
   const void* residual;  // T[M][N] or null (may alias c)
+  uint32_t out_scale;    // 0, or 0x10000 | bits of T(scale): last post-op
   int m, n, k;
   int n_tiles, m_tiles, kblks;
   int dbg;  // tuning only: bit0 = dequantisers skip the conversion, bit1 = MMA issuer skips the MMAs
@@ -331,6 +332,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
                 const size_t off = static_cast<size_t>(tok) * p.n + n;
                 if (rbase) o = __hadd(rbase[off], o);
                 if (p.bias) o = __hadd(o, bias_v);
+                o = apply_out_scale<T>(o, p.out_scale);
                 cbase[off] = o;
               }
             }
@@ -386,6 +388,8 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
           for (int i = 0; i < 4; ++i) o[i] = __hadd(o[i], bs[i]);
         }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) o[i] = apply_out_scale<T>(o[i], p.out_scale);
         uint2 pk;
         pk.x = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[0])) |
                (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[1])) << 16);

@@ -26,6 +26,7 @@ struct StreamArgs {
   const void* scales;    // raw pointer (channelwise epilogue)
   const void* bias;      // T[N] or null
   const void* residual;  // T[M][N] or null
+  uint32_t out_scale;    // 0, or 0x10000 | bits of T(scale): last post-op
   int m, n, k;
   int kblks;             // K / KB
   int dbg_skip;          // tuning only: 1 = consumers release stages without computing (memory-pipeline ceiling)
@@ -297,6 +298,8 @@ w4a16_stream_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
 #pragma unroll
         for (int i = 0; i < 4; ++i) o[i] = __hadd(o[i], bs[i]);
       }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) o[i] = apply_out_scale<T>(o[i], p.out_scale);
       uint2 pk;
       pk.x = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[0])) |
              (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[1])) << 16);

@@ -37,12 +37,44 @@ bool g_stream_v2 = [] {
   return e ? (e[0] == '1') : false;
 }();
 
+// Per-shape mix of the two streaming kernels (B200_W4A16_STREAM_V2 unset): the cluster split-K kernel
+// reduces through DSMEM (about 1 us) where the persistent stream-K kernel ends in a cross-CTA reduction
+// through L2 (2.5-4 us), so it wins while a launch streams few bytes; the persistent kernel wins on the
+// big shapes (no wave quantisation).  Thresholds in int4 weight bytes (K*N/2) for M <= 8 / 9..16 / 17..32,
+// from the B200 measurements in profiles/r01 (b_bench_ours_stream_v2.json against g_bench_ours_final.json
+// and the i_* mixed-chain runs); 0 = never.
+long long g_mix_bytes[3] = {
+    [] { const char* e = std::getenv("B200_W4A16_MIX_BYTES_M8"); return e ? std::atoll(e) : 0ll; }(),
+    [] { const char* e = std::getenv("B200_W4A16_MIX_BYTES_M16"); return e ? std::atoll(e) : 0ll; }(),
+    [] { const char* e = std::getenv("B200_W4A16_MIX_BYTES_M32"); return e ? std::atoll(e) : 0ll; }(),
+};
+bool g_stream_v2_forced = std::getenv("B200_W4A16_STREAM_V2") != nullptr;
+bool use_cluster_streamer(int mm, long long n, long long k) {
+  if (g_stream_v2_forced) return g_stream_v2;
+  const long long bytes = n * k / 2;
+  const long long thr = g_mix_bytes[mm <= 8 ? 0 : (mm <= 16 ? 1 : 2)];
+  return bytes <= thr;
+}
+
 // cap on resident CTAs per SM of the first-generation persistent streaming kernel
 int g_v1_occ = [] {
   const char* e = std::getenv("B200_W4A16_V1_OCC");
   const int v = e ? std::atoi(e) : 1;
   return v < 1 ? 1 : (v > 4 ? 4 : v);
 }();
+
+uint32_t out_scale_bits(float v, int dtype) {
+  if (v == 0.0f) return 0u;
+  uint16_t u;
+  if (dtype == 0) {
+    const __half h = __float2half_rn(v);  // T(v), as elementwise_scale_kernel rounds it (elementwise.cuh:39)
+    std::memcpy(&u, &h, 2);
+  } else {
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    std::memcpy(&u, &h, 2);
+  }
+  return 0x10000u | u;
+}
 
 int fail(int code, const char* fmt, ...) {
   char buf[1024];
@@ -208,6 +240,7 @@ int launch_decode(const GemmCall& g) {
   args.scales = g.scales;
   args.bias = g.bias;
   args.residual = g.residual;
+  args.out_scale = out_scale_bits(g.out_scale, g.dtype);
   args.m = g.m;
   args.n = g.n;
   args.k = g.k;
@@ -405,7 +438,7 @@ int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int 
     return prefill_id(tile, S);
   }
   const int mm = static_cast<int>(m < 32 ? m : 32);
-  if (g_stream_v2) {
+  if (use_cluster_streamer(mm, n, k)) {
     GemmCall g;
     std::memset(&g, 0, sizeof(g));
     g.m = mm;
@@ -511,6 +544,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     g.c_tmp = c_tmp;
     g.bias = opts ? opts->bias : nullptr;
     g.residual = opts ? opts->residual : nullptr;
+    g.out_scale = opts ? opts->out_scale : 0.0f;
     g.m = static_cast<int>(m);
     g.n = static_cast<int>(n);
     g.k = static_cast<int>(k);
@@ -535,7 +569,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
   for (int64_t m0 = 0; m0 < m; m0 += 32) {
     const int mm = static_cast<int>(m - m0 < 32 ? m - m0 : 32);
     int idx = -1;
-    if (forced >= kStreamBase || (forced == 0 && g_stream_v2)) {
+    if (forced >= kStreamBase || (forced == 0 && use_cluster_streamer(mm, n, k))) {
       // cluster split-K streaming kernel
     } else if (opts && opts->force_config > 0) {
       idx = opts->force_config - 1;
@@ -558,6 +592,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     g.residual = (opts && opts->residual)
                      ? static_cast<const char*>(opts->residual) + static_cast<size_t>(m0) * n * esz
                      : nullptr;
+    g.out_scale = opts ? opts->out_scale : 0.0f;
     g.m = mm;
     g.n = static_cast<int>(n);
     g.k = static_cast<int>(k);

@@ -102,8 +102,10 @@ template <typename T, bool SCALED>
 int dispatch_nt(const DenseCall& g) {
   // 64-row tiles while the token block is small; 128 / 256-row tiles beyond, so that the activation boxes
   // re-read from L2 every stage stay at most a quarter of the bytes of the weight boxes
-  if (g.m <= 8) return launch_dense<T, 1, 64, 128, 8, SCALED>(g);
-  if (g.m <= 16) return launch_dense<T, 2, 64, 128, 8, SCALED>(g);
+  // few rows (EAGLE fc1 / fc2, 4096 outputs): 32-row tiles, so that more SMs than N / 64 take part
+  const bool small_n = (g.n + 63) / 64 < 2 * sm_count();
+  if (g.m <= 8) return small_n ? launch_dense<T, 1, 32, 128, 8, SCALED>(g) : launch_dense<T, 1, 64, 128, 8, SCALED>(g);
+  if (g.m <= 16) return small_n ? launch_dense<T, 2, 32, 128, 8, SCALED>(g) : launch_dense<T, 2, 64, 128, 8, SCALED>(g);
   if (g.m <= 32) return launch_dense<T, 4, 128, 128, 4, SCALED>(g);
   return launch_dense<T, 8, 256, 64, 4, SCALED>(g);
 }

@@ -98,6 +98,7 @@ int launch_one(const GemmCall& g, int S, int* query) {
   args.scales = g.scales;
   args.bias = g.bias;
   args.residual = g.residual;
+  args.out_scale = out_scale_bits(g.out_scale, g.dtype);
   args.m = g.m;
   args.n = g.n;
   args.k = g.k;

@@ -45,13 +45,19 @@ extern "C" {
 typedef struct b200_w4a16_opts {
   /* post-ops of W4A16GPTQMarlinLinear::prefill (src/model/w4a16_gptq_marlin/w4a16_gptq_marlin_linear.cuh:140-145),
    * fused into the GEMM epilogue with the reference's rounding points:
-   *   out = RN_T(gemm);  if (residual) out = RN_T(residual + out);  if (bias) out = RN_T(out + bias)   */
+   *   out = RN_T(gemm);  if (residual) out = RN_T(residual + out);  if (bias) out = RN_T(out + bias);
+   *   if (out_scale) out = RN_T(out * T(out_scale))   */
   const void* bias;      /* T[N] or NULL                        (batched_add, src/model/elementwise.cuh:8-14)  */
   const void* residual;  /* T[M][N] or NULL; may alias `c`      (elementwise_add, src/model/elementwise.cuh:17-23) */
   int64_t c_tmp_bytes;   /* size of c_tmp if known (validated), or 0 = caller guarantees b200_w4a16_reduce_bytes() */
   int force_config;      /* 0 = heuristic; >0 = kernel configuration id (tuning / tests only)        */
   int pdl;               /* 1 = launch with programmatic dependent launch (prologue overlaps the previous kernel) */
-  int reserved[5];
+  /* residual scaling of the layer (elementwise_scale(output, residual_scale) right after o_proj / before the
+   * next layer reads down_proj's output, src/model/w4a16_gptq_marlin/w4a16_gptq_marlin_layer.cuh:57,71,79,93;
+   * kernel src/model/elementwise.cuh:35-41), fused as the LAST post-op with the reference's rounding:
+   *   out = RN_T(out * T(out_scale)).   0 (zero-initialised opts) = no scaling. */
+  float out_scale;
+  int reserved[4];
 } b200_w4a16_opts;
 
 /* Replaces gptq_marlin_gemm<T> (src/qgemm/gptq_marlin/gptq_marlin.cuh:11-27, gptq_marlin.cu:42-86)

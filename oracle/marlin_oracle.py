@@ -224,7 +224,7 @@ def gemm(a: np.ndarray, qweight: np.ndarray, scales_marlin: np.ndarray, size_k: 
 
 
 def linear_forward(a, qweight, scales_marlin, size_k, size_n, group_size=128, dtype=FP16,
-                   bias=None, tgt=None, inplace=False):
+                   bias=None, tgt=None, inplace=False, out_scale=0.0):
     """W4A16GPTQMarlinLinear::prefill post-ops (w4a16_gptq_marlin_linear.cuh:104-146):
     inplace -> tgt = tgt + out (elementwise.cuh:17-23, computed in T), has_bias -> tgt += bias."""
     out, _ = gemm(a, qweight, scales_marlin, size_k, size_n, group_size, dtype)
@@ -234,6 +234,12 @@ def linear_forward(a, qweight, scales_marlin, size_k, size_n, group_size=128, dt
         res = to_f32(to_storage(to_f32(np.asarray(tgt), dtype) + res, dtype), dtype)
     if bias is not None:
         res = to_f32(to_storage(res + to_f32(np.asarray(bias), dtype)[None, :], dtype), dtype)
+    if out_scale:
+        # the layer's residual scaling, applied to the stored output afterwards: out = out * T(v), both in T
+        # (elementwise_scale_kernel, src/model/elementwise.cuh:35-41; call sites
+        # w4a16_gptq_marlin_layer.cuh:57,71,79,93).  The fp32 product of two T values is exact -> one RN.
+        sv = to_f32(to_storage(np.array([out_scale], dtype=np.float32), dtype), dtype)[0]
+        res = to_f32(to_storage(res * sv, dtype), dtype)
     return to_storage(res, dtype)
 
 

@@ -309,6 +309,37 @@ def test_linear_operator_postops_tcgen05():
     assert st["max_rel"] <= TOL_MAX_REL, st
 
 
+@pytest.mark.parametrize("tdt", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("m,force", [(1, 0), (5, 0), (12, 0), (24, 0), (32, 0), (7, 2001), (16, 2002), (64, 0), (200, 0),
+                                     (700, 0)])
+def test_out_scale_postop(tdt, m, force):
+    """The layer's residual scaling fused as the last post-op (elementwise_scale on the o_proj / down_proj output,
+    w4a16_gptq_marlin_layer.cuh:57,71,79,93; kernel elementwise.cuh:35-41): exactly the reference's rounding
+    sequence applied to the kernel's own GEMM output, RN(RN(RN(res + gemm) + bias) * T(scale)), bit for bit,
+    on every kernel family (persistent stream-K, cluster split-K [forced], tcgen05 split-K and whole-K)."""
+    b = _b()
+    k, n = 512, 640
+    dtype = mo.FP16 if tdt == torch.float16 else mo.BF16
+    prob = mo.make_problem(m, k, n, 128, dtype, seed=31 + m)
+    a, qw, sc = t_store(prob["a"], dtype), torch.from_numpy(prob["qweight"]).to(DEV), t_store(prob["scales_marlin"], dtype)
+    g = torch.Generator(device=DEV).manual_seed(m)
+    res = torch.randn((m, n), generator=g, device=DEV, dtype=torch.float32).to(tdt)
+    bias = torch.randn((n,), generator=g, device=DEV, dtype=torch.float32).to(tdt)
+    scale = 1.4 / np.sqrt(32.0)       # MiniCPM4-8B: scale_depth / sqrt(num_hidden_layers)
+    ws, c_tmp = scratch(m, n, k)
+    plain = b.gemm(a, qw, sc, ws, c_tmp, force_config=force)
+    got = b.gemm(a, qw, sc, ws, c_tmp, residual=res, bias=bias, out_scale=scale, force_config=force)
+    only = b.gemm(a, qw, sc, ws, c_tmp, out_scale=scale, force_config=force)
+    torch.cuda.synchronize()
+    sv = torch.tensor(scale, dtype=torch.float32, device=DEV).to(tdt)
+    assert torch.equal(got, ((res + plain) + bias) * sv)
+    assert torch.equal(only, plain * sv)
+    assert int(ws.abs().max()) == 0
+    want = mo.linear_forward(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, dtype, out_scale=scale)
+    st = mo.error_stats(t_load(only, dtype), mo.to_f32(want, dtype).astype(np.float64), dtype)
+    assert st["max_rel"] <= TOL_MAX_REL, st
+
+
 def test_error_convention():
     b = _b()
     a = torch.zeros((1, 128), dtype=torch.float16, device=DEV)
