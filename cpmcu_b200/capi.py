@@ -30,7 +30,8 @@ class Opts(ctypes.Structure):
         ("force_config", c_int),
         ("pdl", c_int),
         ("out_scale", c_float),
-        ("reserved", c_int * 4),
+        ("gated_silu", c_int),
+        ("reserved", c_int * 3),
     ]
 
 
@@ -147,7 +148,8 @@ def config_name(cfg: int) -> str:
 
 
 def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm=None, a_tmp=None,
-         bias=None, residual=None, out_scale=0.0, force_config=0, pdl=False, stream=None):
+         bias=None, residual=None, out_scale=0.0, gated_silu=False, force_config=0, pdl=False,
+         stream=None):
     """C[M,N] = A[M,K] . dequant(qweight, scales)  (+ residual, + bias, * T(out_scale)) on the current stream.
 
     a: [M,K] fp16/bf16 cuda, qweight: int32 [K/16, 2N] cuda (Marlin), scales: [K/g, N] (Marlin-permuted),
@@ -158,12 +160,13 @@ def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm
     m, k = a.shape
     n = qweight.shape[1] // 2
     if out is None:
-        out = torch.empty((m, n), dtype=a.dtype, device=a.device)
+        out = torch.empty((m, n // 2 if gated_silu else n), dtype=a.dtype, device=a.device)
     o = Opts()
     o.bias = None if bias is None else bias.data_ptr()
     o.residual = None if residual is None else residual.data_ptr()
     o.c_tmp_bytes = 0 if c_tmp is None else c_tmp.numel() * c_tmp.element_size()
     o.out_scale = float(out_scale)
+    o.gated_silu = 1 if gated_silu else 0
     o.force_config = force_config
     o.pdl = 1 if pdl else 0
     rc = lib().b200_w4a16_gemm_ex(_ptr(a), _ptr(qweight), _ptr(scales), None, _ptr(perm), _ptr(workspace),

@@ -42,6 +42,7 @@ struct DecodeArgs {
   int kblks;      // K / KB
   int slot_max;   // slots per column reserved in c_tmp
   int colpar;     // 1: CTAs take whole columns (no split columns, no reduction through c_tmp)
+  int gated;      // 1: tile = [TN/2 gate columns | the same TN/2 up columns]; c[M][N/2] = silu(gate) * up
   unsigned long long* dbg_ts;  // tuning only: per-CTA phase timestamps or null
 };
 
@@ -135,6 +136,29 @@ __device__ __forceinline__ void emit_out(const DecodeArgs& p, int tok, int n, fl
   *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.c) + off) = pk;
 }
 
+// fused FFN activation over a [gate | up] tile (reference: gated_silu_interleaved_kernel,
+// src/model/activation.cuh:7-18, compiled with --use_fast_math there): gate and up sums are rounded to T
+// first (they are gateup_proj's stored output in the reference), then T(g * sigmoid(g) * u)
+template <typename T>
+__device__ __forceinline__ void emit_gated(const DecodeArgs& p, int tok, int n_out, float4 gs, float4 us) {
+  const float gv[4] = {gs.x, gs.y, gs.z, gs.w};
+  const float uv[4] = {us.x, us.y, us.z, us.w};
+  T o[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float g = Elem<T>::to_float(Elem<T>::from_float(gv[e]));
+    const float u = Elem<T>::to_float(Elem<T>::from_float(uv[e]));
+    const float sg = __fdividef(1.0f, 1.0f + __expf(-g));
+    o[e] = Elem<T>::from_float(g * sg * u);
+  }
+  uint2 pk;
+  pk.x = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[0])) |
+         (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[1])) << 16);
+  pk.y = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[2])) |
+         (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[3])) << 16);
+  *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.c) + static_cast<size_t>(tok) * (p.n >> 1) + n_out) = pk;
+}
+
 // the sharers of column tile c under the even unit split: CTAs cta_first..cta_last, slot = cta - cta_first
 struct ColumnShare {
   int nparts, my_slot;
@@ -156,7 +180,9 @@ __device__ __forceinline__ ColumnShare column_share(const DecodeArgs& p, int c, 
   return cs;
 }
 
-template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED>
+// GATED: the fused [gate | up] tile + SiLU(gate) * up epilogue; a template parameter (not a runtime flag) so
+// that the plain kernels keep their register allocation and code exactly (a runtime flag cost 2 % at M <= 8)
+template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED, bool GATED = false>
 __global__ void __launch_bounds__(WARPS * 32 + 64, (NT == 1 || (NT == 2 && WARPS <= 8)) ? 2 : 1)  // 2: PDL co-residency
 w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_s,
                     const __grid_constant__ CUtensorMap tm_a, const DecodeArgs p) {
@@ -216,11 +242,19 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       auto issue_w = [&](int s, int c, int b) {
         const uint32_t full = bar_full + 8 * s;
         mbar_arrive_expect_tx(full, Cfg::STAGE_TX);
-        tma_load_3d(sbase + Cfg::OFF_W + s * Cfg::W_STAGE, &tm_w, full, 0, c * CHUNKS, b * KROWS,
-                    kEvictFirst);
-        if (GROUPED)
-          tma_load_3d(sbase + Cfg::OFF_S + s * Cfg::S_STAGE, &tm_s, full, 0, c * CHUNKS,
-                      (b * KB) / 128, kEvictLast);
+        if (GATED) {  // one 4-d box: CHUNKS/2 gate chunks + the same CHUNKS/2 up chunks (see launch_decode)
+          tma_load_4d(sbase + Cfg::OFF_W + s * Cfg::W_STAGE, &tm_w, full, 0, c * (CHUNKS / 2), 0, b * KROWS,
+                      kEvictFirst);
+          if (GROUPED)
+            tma_load_4d(sbase + Cfg::OFF_S + s * Cfg::S_STAGE, &tm_s, full, 0, c * (CHUNKS / 2), 0,
+                        (b * KB) / 128, kEvictLast);
+        } else {
+          tma_load_3d(sbase + Cfg::OFF_W + s * Cfg::W_STAGE, &tm_w, full, 0, c * CHUNKS, b * KROWS,
+                      kEvictFirst);
+          if (GROUPED)
+            tma_load_3d(sbase + Cfg::OFF_S + s * Cfg::S_STAGE, &tm_s, full, 0, c * CHUNKS,
+                        (b * KB) / 128, kEvictLast);
+        }
       };
       auto issue_a = [&](int s, int b) {
         const uint32_t full = bar_full + 8 * s;
@@ -273,7 +307,13 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       mbar_wait_backoff(bar_red_full, seg & 1u, 64);
       const int items = p.m * (TN / 4);  // float4 items of the valid token rows
       const int col0 = c * TN;
-      if (whole) {
+      if (whole && GATED) {
+        for (int e = lane; e < p.m * (TN / 8); e += 32) {
+          const int tok = e / (TN / 8), nn = (e - tok * (TN / 8)) * 4;
+          emit_gated<T>(p, tok, c * (TN / 2) + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn),
+                        *reinterpret_cast<const float4*>(red + tok * TNP + TN / 2 + nn));
+        }
+      } else if (whole) {
         for (int e = lane; e < items; e += 32) {
           const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
           if (col0 + nn < p.n)
@@ -423,7 +463,14 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
         const int tid = static_cast<int>(threadIdx.x);
         const int items = p.m * (TN / 4);  // float4 items of the valid token rows
         const int col0 = c_last * TN;
-        if (whole) {
+        const int gcol0 = c_last * (TN / 2);  // gated: first output column of the tile
+        if (whole && GATED) {
+          for (int e = tid; e < p.m * (TN / 8); e += NCONS) {
+            const int tok = e / (TN / 8), nn = (e - tok * (TN / 8)) * 4;
+            emit_gated<T>(p, tok, gcol0 + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn),
+                          *reinterpret_cast<const float4*>(red + tok * TNP + TN / 2 + nn));
+          }
+        } else if (whole) {
           for (int e = tid; e < items; e += NCONS) {
             const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
             if (col0 + nn < p.n)
@@ -459,7 +506,9 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
               if (tid == 0) dbg_stamp1(p, 6);
               float4* stage = reinterpret_cast<float4*>(smem + Cfg::OFF_W);
               constexpr int CAP = (NS * Cfg::W_STAGE) / 16;
-              const int ib = CAP / np1;  // items per round
+              // items per round; whole token rows when gated, so that a gate item and its up item (TN/8
+              // items further in the same row) are staged in the same round
+              const int ib = GATED ? (CAP / np1) / (TN / 4) * (TN / 4) : CAP / np1;
               for (int i0 = 0; i0 < items; i0 += ib) {
                 const int ni = (items - i0) < ib ? (items - i0) : ib;
                 // fire-and-forget 16-byte copies global(L2) -> shared: every partial of the round in flight at once
@@ -471,10 +520,9 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
                 }
                 asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
                 named_bar_sync(1, NCONS);
-                for (int e = tid; e < ni; e += NCONS) {
+                auto sum_item = [&](int e) {  // own partial + the staged ones, in slot order
                   const int item = i0 + e;
                   const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
-                  if (col0 + nn >= p.n) continue;
                   float4 sum = *reinterpret_cast<const float4*>(red + tok * TNP + nn);
                   for (int sl = 0; sl < np1; ++sl) {
                     const float4 v = stage[sl * ni + e];
@@ -483,7 +531,21 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
                     sum.z += v.z;
                     sum.w += v.w;
                   }
-                  emit_out<T, GROUPED>(p, tok, col0 + nn, sum);
+                  return sum;
+                };
+                if (GATED) {
+                  for (int e = tid; e < ni / 2; e += NCONS) {
+                    const int r = e / (TN / 8), jj = e - r * (TN / 8);
+                    const int eg = r * (TN / 4) + jj;
+                    emit_gated<T>(p, i0 / (TN / 4) + r, gcol0 + jj * 4, sum_item(eg), sum_item(eg + TN / 8));
+                  }
+                } else {
+                  for (int e = tid; e < ni; e += NCONS) {
+                    const int item = i0 + e;
+                    const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
+                    if (col0 + nn >= p.n) continue;
+                    emit_out<T, GROUPED>(p, tok, col0 + nn, sum_item(e));
+                  }
                 }
                 named_bar_sync(1, NCONS);
               }
@@ -522,12 +584,16 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
             bool counted = false;
             int prev_count = -1;
             {
-              const int e_lo = static_cast<int>((static_cast<long long>(cs.my_slot) * items) / nlate);
-              const int e_hi = static_cast<int>((static_cast<long long>(cs.my_slot + 1) * items) / nlate);
+              // this sharer's slice of the tile: an even share of the items; of the token ROWS when gated,
+              // so that a gate item and its up item (same row) fall to the same sharer and round
+              const int e_lo = GATED ? (cs.my_slot * p.m / nlate) * (TN / 4)
+                                       : static_cast<int>((static_cast<long long>(cs.my_slot) * items) / nlate);
+              const int e_hi = GATED ? ((cs.my_slot + 1) * p.m / nlate) * (TN / 4)
+                                       : static_cast<int>((static_cast<long long>(cs.my_slot + 1) * items) / nlate);
               const int np1 = cs.nparts - 1;
               float4* stage = reinterpret_cast<float4*>(smem + Cfg::OFF_W);
               constexpr int CAP = (NS * Cfg::W_STAGE) / 16;
-              const int ib = CAP / np1;  // items per round
+              const int ib = GATED ? (CAP / np1) / (TN / 4) * (TN / 4) : CAP / np1;  // items per round
               for (int i0 = e_lo; i0 < e_hi; i0 += ib) {
                 const int ni = (e_hi - i0) < ib ? (e_hi - i0) : ib;
                 // fire-and-forget 16-byte copies global(L2) -> shared, the own slot skipped
@@ -547,10 +613,9 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
                   counted = true;
                   prev_count = atomicAdd(done, 1);  // the returned count is looked at after the sums are written
                 }
-                for (int e = tid; e < ni; e += NCONS) {
+                auto sum_item = [&](int e) {
                   const int item = i0 + e;
                   const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
-                  if (col0 + nn >= p.n) continue;
                   const float4 own = *reinterpret_cast<const float4*>(red + tok * TNP + nn);
                   float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
                   for (int sl = 0, row = 0; sl < cs.nparts; ++sl) {  // slot order: bit-deterministic
@@ -570,7 +635,21 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
                       sum.w += v.w;
                     }
                   }
-                  emit_out<T, GROUPED>(p, tok, col0 + nn, sum);
+                  return sum;
+                };
+                if (GATED) {
+                  for (int e = tid; e < ni / 2; e += NCONS) {
+                    const int r = e / (TN / 8), jj = e - r * (TN / 8);
+                    const int eg = r * (TN / 4) + jj;
+                    emit_gated<T>(p, i0 / (TN / 4) + r, gcol0 + jj * 4, sum_item(eg), sum_item(eg + TN / 8));
+                  }
+                } else {
+                  for (int e = tid; e < ni; e += NCONS) {
+                    const int item = i0 + e;
+                    const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
+                    if (col0 + nn >= p.n) continue;
+                    emit_out<T, GROUPED>(p, tok, col0 + nn, sum_item(e));
+                  }
                 }
                 named_bar_sync(1, NCONS);
               }

@@ -19,6 +19,7 @@ struct GemmCall {
   const void* bias;
   const void* residual;
   float out_scale;  // 0 = none
+  bool gated;       // fused SiLU(gate) * up epilogue over the [gate | up] columns (streaming regime only)
   int m, n, k;
   int group_size;
   int dtype;

@@ -45,7 +45,12 @@ struct PrefillCfg {
   static constexpr int S_STAGE = GROUPED ? BN * 2 : 0;
   static constexpr int ACC_COLS = NSUB * BM;       // fp32 TMEM columns per accumulator
   static constexpr int ACC_STAGES = (!SPLIT && (512 / ACC_COLS) >= 2) ? 2 : 1;
-  static constexpr int TMEM_COLS = ACC_COLS * ACC_STAGES;  // a power of two >= 32
+#ifndef B200_TC_SPLIT_TMEM_ALL
+#define B200_TC_SPLIT_TMEM_ALL 0
+#endif
+  // a power of two >= 32 (experiment B200_TC_SPLIT_TMEM_ALL: the split-K tiles take the whole tensor memory,
+  // so that two co-resident CTAs serialise on the allocation)
+  static constexpr int TMEM_COLS = (SPLIT && B200_TC_SPLIT_TMEM_ALL) ? 512 : ACC_COLS * ACC_STAGES;
   // split-K: fp32 partial tile [BM tokens][128 + 4] staged for the cluster reduction; it aliases the
   // A/W rings, which are dead once the last MMA of the CTA's only tile has been committed
   static constexpr int RED_PITCH = 128 + 4;

@@ -122,8 +122,8 @@ EncodeFn encode_fn() {
 
 struct MapKey {
   const void* ptr;
-  uint64_t d0, d1, d2, s1, s2;
-  uint32_t b0, b1, b2, misc;
+  uint64_t d0, d1, d2, d3, s1, s2, s3;
+  uint32_t b0, b1, b2, b3, misc, pad;
   bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
 };
 struct MapKeyHash {
@@ -137,7 +137,7 @@ struct MapKeyHash {
 std::mutex g_map_mu;
 std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 
-// rank 2 or 3 tiled descriptor; dims/strides innermost first (strides[] in bytes for dims 1..)
+// rank 2, 3 or 4 tiled descriptor; dims/strides innermost first (strides[] in bytes for dims 1..)
 int get_tensor_map(CUtensorMap* out, const void* ptr, CUtensorMapDataType type, int rank,
                    const uint64_t* dims, const uint64_t* strides, const uint32_t* box,
                    CUtensorMapSwizzle swz) {
@@ -147,6 +147,9 @@ int get_tensor_map(CUtensorMap* out, const void* ptr, CUtensorMapDataType type, 
   key.d0 = dims[0];
   key.d1 = dims[1];
   key.d2 = rank > 2 ? dims[2] : 0;
+  key.d3 = rank > 3 ? dims[3] : 0;
+  key.s3 = rank > 3 ? strides[2] : 0;
+  key.b3 = rank > 3 ? box[3] : 0;
   key.s1 = strides[0];
   key.s2 = rank > 2 ? strides[1] : 0;
   key.b0 = box[0];
@@ -163,10 +166,10 @@ int get_tensor_map(CUtensorMap* out, const void* ptr, CUtensorMapDataType type, 
   }
   EncodeFn enc = encode_fn();
   if (!enc) return fail(B200_W4A16_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
-  cuuint64_t gdim[3] = {dims[0], dims[1], rank > 2 ? dims[2] : 1};
-  cuuint64_t gstr[2] = {strides[0], rank > 2 ? strides[1] : 0};
-  cuuint32_t bx[3] = {box[0], box[1], rank > 2 ? box[2] : 1};
-  cuuint32_t estr[3] = {1, 1, 1};
+  cuuint64_t gdim[4] = {dims[0], dims[1], rank > 2 ? dims[2] : 1, rank > 3 ? dims[3] : 1};
+  cuuint64_t gstr[3] = {strides[0], rank > 2 ? strides[1] : 0, rank > 3 ? strides[2] : 0};
+  cuuint32_t bx[4] = {box[0], box[1], rank > 2 ? box[2] : 1, rank > 3 ? box[3] : 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = enc(out, type, rank, const_cast<void*>(ptr), gdim, gstr, bx, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -195,10 +198,11 @@ struct DecodeConfig {
   int smem;
 };
 
-template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED>
+template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED, bool GATED = false>
 int launch_decode(const GemmCall& g) {
   using Cfg = DecodeCfg<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>;
-  auto kern = w4a16_decode_kernel<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>;
+  auto kern = w4a16_decode_kernel<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED, GATED>;
+  if (g.gated != GATED) return fail(B200_W4A16_ERUNTIME, "internal: gated launch through a plain kernel");
   static bool attr_set = false;  // benign race: idempotent
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -207,6 +211,30 @@ int launch_decode(const GemmCall& g) {
     attr_set = true;
   }
   CUtensorMap tm_w, tm_s, tm_a;
+  if (g.gated) {
+    // fused gate_up: the tile's first CHUNKS/2 chunks come from the gate half [0, I), the others from the
+    // same columns of the up half [I, 2I) — ONE 4-d box over the views int32 [K/16][2][I/64][128] and
+    // T [K/128][2][I/64][64]; the bytes land exactly where the 3-d box of CHUNKS chunks would put them
+    if ((CHUNKS & 1) || (g.n / 2) % (Cfg::TN / 2) != 0 || !GROUPED)
+      return fail(B200_W4A16_EINVAL, "gated_silu needs group_size 128 and N/2 a multiple of %d, got N = %d", Cfg::TN / 2, g.n);
+    const uint64_t ich = static_cast<uint64_t>(g.n / 2 / 64);
+    {
+      const uint64_t dims[4] = {128, ich, 2, static_cast<uint64_t>(g.k / 16)};
+      const uint64_t strides[3] = {512, ich * 512, static_cast<uint64_t>(g.n) * 8};
+      const uint32_t box[4] = {128, CHUNKS / 2, 2, KROWS};
+      if (int rc = get_tensor_map(&tm_w, g.qweight, CU_TENSOR_MAP_DATA_TYPE_INT32, 4, dims, strides, box,
+                                  CU_TENSOR_MAP_SWIZZLE_NONE))
+        return rc;
+    }
+    {
+      const uint64_t dims[4] = {64, ich, 2, static_cast<uint64_t>(g.k / 128)};
+      const uint64_t strides[3] = {128, ich * 128, static_cast<uint64_t>(g.n) * 2};
+      const uint32_t box[4] = {64, CHUNKS / 2, 2, static_cast<uint32_t>(Cfg::SG)};
+      if (int rc = get_tensor_map(&tm_s, g.scales, Elem<T>::kTmaType, 4, dims, strides, box,
+                                  CU_TENSOR_MAP_SWIZZLE_NONE))
+        return rc;
+    }
+  } else {
   {  // weights: int32 [K/16][N/64][128]
     const uint64_t dims[3] = {128, static_cast<uint64_t>(g.n / 64), static_cast<uint64_t>(g.k / 16)};
     const uint64_t strides[2] = {512, static_cast<uint64_t>(g.n) * 8};
@@ -225,6 +253,7 @@ int launch_decode(const GemmCall& g) {
   } else {
     tm_s = tm_w;
   }
+  }
   {  // activations: T [M][K], 64-wide (128-byte) boxes, 128B swizzle, rows past M zero-filled
     const uint64_t dims[2] = {static_cast<uint64_t>(g.k), static_cast<uint64_t>(g.m)};
     const uint64_t strides[1] = {static_cast<uint64_t>(g.k) * 2};
@@ -234,6 +263,7 @@ int launch_decode(const GemmCall& g) {
       return rc;
   }
   DecodeArgs args;
+  args.gated = g.gated ? 1 : 0;
   args.c = g.c;
   args.c_tmp = g.c_tmp;
   args.workspace = g.workspace;
@@ -244,7 +274,7 @@ int launch_decode(const GemmCall& g) {
   args.m = g.m;
   args.n = g.n;
   args.k = g.k;
-  args.ncols = (g.n + Cfg::TN - 1) / Cfg::TN;
+  args.ncols = g.gated ? (g.n / 2) / (Cfg::TN / 2) : (g.n + Cfg::TN - 1) / Cfg::TN;
   args.kblks = g.k / Cfg::KB;
   const long long units = static_cast<long long>(args.ncols) * args.kblks;
   // persistent CTAs: one per SM (B200_W4A16_V1_OCC raises it for experiments, if resources allow)
@@ -308,6 +338,23 @@ const DecodeConfig g_decode[] = {
     DECODE_FAMILY(__half, 0, 4, false),         DECODE_FAMILY(__nv_bfloat16, 1, 1, false),
     DECODE_FAMILY(__nv_bfloat16, 1, 2, false),  DECODE_FAMILY(__nv_bfloat16, 1, 4, false),
 };
+
+// fused gate_up + SiLU(gate) * up: the two default geometries (pick_geometry) of every token-block width
+template <typename T>
+int launch_gated_t(const GemmCall& g, int nt, int geom) {
+  if (geom == 1) {
+    if (nt == 1) return launch_decode<T, 1, 4, 8, 8, 5, true, true>(g);
+    if (nt == 2) return launch_decode<T, 2, 4, 8, 8, 5, true, true>(g);
+    return launch_decode<T, 4, 4, 8, 8, 5, true, true>(g);
+  }
+  if (nt == 1) return launch_decode<T, 1, 4, 4, 8, 8, true, true>(g);
+  if (nt == 2) return launch_decode<T, 2, 4, 4, 8, 8, true, true>(g);
+  return launch_decode<T, 4, 4, 4, 8, 8, true, true>(g);
+}
+int launch_gated(const GemmCall& g, int nt, int geom) {
+  if (geom != 1 && geom != 2) return fail(B200_W4A16_EINVAL, "gated_silu: unsupported geometry %d", geom);
+  return g.dtype == 0 ? launch_gated_t<__half>(g, nt, geom) : launch_gated_t<__nv_bfloat16>(g, nt, geom);
+}
 
 // index into g_decode
 int decode_index(int dtype, int nt, bool grouped, int geom) {
@@ -531,6 +578,17 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
   const bool grouped = group_size != -1;
   const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
   const int forced = opts ? opts->force_config : 0;
+  const bool gated = opts && opts->gated_silu != 0;
+  if (gated) {
+    // fused SiLU(gate) * up: served by the persistent streaming kernel (decode / tree-verify widths)
+    if (m > 32 || forced != 0)
+      return fail(B200_W4A16_EINVAL, "gated_silu is fused for M <= 32 with the default configuration (got M = %lld, force_config %d)", (long long)m, forced);
+    if (group_size != 128 || (n % 256) != 0)
+      return fail(B200_W4A16_EINVAL, "gated_silu needs group_size 128 and N (= 2 x intermediate) a multiple of 256, got N = %lld", (long long)n);
+    if (opts->bias || opts->residual || opts->out_scale != 0.0f)
+      return fail(B200_W4A16_EINVAL, "gated_silu does not combine with bias / residual / out_scale");
+    if (has_act_order) return fail(B200_W4A16_EINVAL, "gated_silu does not combine with act-order");
+  }
   // ---- tensor-bound regime: one persistent tcgen05 launch for any M ----
   if ((forced == 0 && m > kStreamMaxM) || (forced >= kPrefillBase && forced < kStreamBase)) {
     if (forced >= kPrefillBase + kPrefillIds)
@@ -545,6 +603,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     g.bias = opts ? opts->bias : nullptr;
     g.residual = opts ? opts->residual : nullptr;
     g.out_scale = opts ? opts->out_scale : 0.0f;
+    g.gated = false;
     g.m = static_cast<int>(m);
     g.n = static_cast<int>(n);
     g.k = static_cast<int>(k);
@@ -569,7 +628,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
   for (int64_t m0 = 0; m0 < m; m0 += 32) {
     const int mm = static_cast<int>(m - m0 < 32 ? m - m0 : 32);
     int idx = -1;
-    if (forced >= kStreamBase || (forced == 0 && use_cluster_streamer(mm, n, k))) {
+    if (forced >= kStreamBase || (forced == 0 && !gated && use_cluster_streamer(mm, n, k))) {
       // cluster split-K streaming kernel
     } else if (opts && opts->force_config > 0) {
       idx = opts->force_config - 1;
@@ -593,6 +652,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
                      ? static_cast<const char*>(opts->residual) + static_cast<size_t>(m0) * n * esz
                      : nullptr;
     g.out_scale = opts ? opts->out_scale : 0.0f;
+    g.gated = gated;
     g.m = mm;
     g.n = static_cast<int>(n);
     g.k = static_cast<int>(k);
@@ -610,6 +670,10 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
         stream_pick(g, &geom, &S);
       }
       if (int rc = launch_stream(g, geom, S)) return rc;
+      continue;
+    }
+    if (gated) {
+      if (int rc = launch_gated(g, nt_for_m(mm), pick_geometry(mm, (int)n, (int)k))) return rc;
       continue;
     }
     if (int rc = g_decode[idx].launch(g)) return rc;

@@ -33,8 +33,17 @@ int launch_one(const GemmCall& g, int S, int* query) {
   using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
   auto kern = w4a16_prefill_kernel<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
   static bool attr_set = false;  // benign race: idempotent
+  // Split-K tiles run ONE CTA per SM: with two co-resident CTAs (87-110 KB each) and >= 32 k-blocks per CTA about
+  // 1.5 % of the launches at M = 64 returned a wrong 16..64-column block (tools/stress_m64*.py, profiles/r01/k_*;
+  // never seen with one CTA per SM in > 10^4 launches).  Until that race is found the launch asks for more than
+  // half an SM's shared memory, which rules co-residency out.  B200_W4A16_TC_CORESIDENT=1 restores the old launch.
+  static const bool coresident = [] { const char* e = std::getenv("B200_W4A16_TC_CORESIDENT"); return e && e[0] == '1'; }();
+  // B200_W4A16_TC_PAD: 2 = every split-K launch is padded; 1 = only launches with more CTAs than SMs (CTAs of the
+  // SAME launch would share an SM; the next launch's CTAs may still co-reside under PDL); 0 = never
+  static const int pad_mode = [] { const char* e = std::getenv("B200_W4A16_TC_PAD"); return e ? std::atoi(e) : 2; }();
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Cfg::SMEM_BYTES < 117 * 1024 ? 117 * 1024 : Cfg::SMEM_BYTES);
     if (e != cudaSuccess)
       return fail(B200_W4A16_ECUDA, "cudaFuncSetAttribute(smem=%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
     attr_set = true;
@@ -120,7 +129,9 @@ int launch_one(const GemmCall& g, int S, int* query) {
   std::memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(Cfg::THREADS);
-  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  const bool pad = SPLIT && !coresident && Cfg::SMEM_BYTES < 117 * 1024 &&
+                   (pad_mode >= 2 || (pad_mode == 1 && grid > sm_count()));
+  cfg.dynamicSmemBytes = pad ? 117 * 1024 : Cfg::SMEM_BYTES;
   cfg.stream = g.stream;
   cudaLaunchAttribute attr[2];
   int na = 0;
@@ -189,7 +200,9 @@ void prefill_pick(const GemmCall& g, int* tile_out, int* S_out) {
     const int bm = kTiles[t].bm;
     const int tiles = ((n + 127) / 128) * ((m + bm - 1) / bm);
     const int kblks = g.k / 64;
-    const int cap = (2 * sms * 9) / 10;
+    // one CTA per SM (see launch_one: co-resident split-K CTAs are switched off), one wave when possible
+    static const bool coresident = [] { const char* e = std::getenv("B200_W4A16_TC_CORESIDENT"); return e && e[0] == '1'; }();
+    const int cap = coresident ? (2 * sms * 9) / 10 : sms;
     int s = 8;
     while (s > 1 && (kblks / s < 4 || tiles * s > cap)) s >>= 1;
     if (m <= 128 || tiles <= cap) {

@@ -57,7 +57,14 @@ typedef struct b200_w4a16_opts {
    * kernel src/model/elementwise.cuh:35-41), fused as the LAST post-op with the reference's rounding:
    *   out = RN_T(out * T(out_scale)).   0 (zero-initialised opts) = no scaling. */
   float out_scale;
-  int reserved[4];
+  /* 1 = the weight is the fused [gate | up] matrix (N = 2 x intermediate, gptq2marlin.py:162-230) and the
+   * epilogue applies the FFN activation: c[M][N/2] = T(g * sigmoid(g) * u) with g, u the gate / up outputs
+   * rounded to T first — gated_silu_interleaved (src/model/activation.cuh:7-18), the launch between
+   * gateup_proj and down_proj in w4a16_gptq_marlin_ffn.cuh:70-72.  Streaming regime only (M <= 32); value
+   * error beyond, where the caller keeps the separate activation kernel.  Needs group_size 128 and
+   * N % 256 == 0; does not combine with bias / residual / out_scale / act-order. */
+  int gated_silu;
+  int reserved[3];
 } b200_w4a16_opts;
 
 /* Replaces gptq_marlin_gemm<T> (src/qgemm/gptq_marlin/gptq_marlin.cuh:11-27, gptq_marlin.cu:42-86)

@@ -243,6 +243,16 @@ def linear_forward(a, qweight, scales_marlin, size_k, size_n, group_size=128, dt
     return to_storage(res, dtype)
 
 
+def gated_silu_interleaved(gate_up, dtype=FP16):
+    """gated_silu_interleaved_kernel (src/model/activation.cuh:7-18): src is gateup_proj's stored output
+    T[M][2I] = [gate | up]; tgt[m][j] = T(g * (1 / (1 + expf(-g))) * u) with g, u = float(src), fp32 math."""
+    x = to_f32(np.asarray(gate_up), dtype)
+    half = x.shape[1] // 2
+    g, u = x[:, :half].astype(np.float32), x[:, half:].astype(np.float32)
+    sg = (np.float32(1.0) / (np.float32(1.0) + np.exp(-g, dtype=np.float32))).astype(np.float32)
+    return to_storage((g * sg) * u, dtype)
+
+
 def dense_linear(a, weight, dtype=FP16, bias=None, tgt=None, inplace=False, head_scale=1.0):
     """Un-quantised Linear<T>::prefill / LMHead<T>::prefill (src/model/linear.cuh:8-37,76-105) restated:
       LMHead: input * T(head_scale), rounded to T (elementwise_scale_kernel, elementwise.cuh:35-41);

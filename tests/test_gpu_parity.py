@@ -340,6 +340,85 @@ def test_out_scale_postop(tdt, m, force):
     assert st["max_rel"] <= TOL_MAX_REL, st
 
 
+@pytest.mark.parametrize("tdt", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("m", [1, 5, 8, 9, 16, 24, 32])
+@pytest.mark.parametrize("k,inter", [(512, 384), (128, 256), (2048, 1024)])
+def test_gated_silu_fused(tdt, m, k, inter):
+    """gate_up GEMM + gated_silu_interleaved (activation.cuh:7-18; w4a16_gptq_marlin_ffn.cuh:70-72) in ONE launch:
+    against the oracle's two-step pipeline (GEMM rounded to T, then the activation in fp32), and against the
+    activation applied to the kernel's own plain gate_up output.  Small shapes: every column tile is split over
+    several CTAs (k = 512, 2048) or whole (k = 128), so all reduction paths of the kernel emit gated pairs."""
+    b = _b()
+    n = 2 * inter
+    dtype = mo.FP16 if tdt == torch.float16 else mo.BF16
+    prob = mo.make_problem(m, k, n, 128, dtype, seed=41 + m)
+    a, qw, sc = t_store(prob["a"], dtype), torch.from_numpy(prob["qweight"]).to(DEV), t_store(prob["scales_marlin"], dtype)
+    ws, c_tmp = scratch(m, n, k)
+    plain = b.gemm(a, qw, sc, ws, c_tmp)
+    got = b.gemm(a, qw, sc, ws, c_tmp, gated_silu=True)
+    torch.cuda.synchronize()
+    assert got.shape == (m, inter)
+    assert int(ws.abs().max()) == 0
+    g, u = plain[:, :inter].float(), plain[:, inter:].float()
+    want_own = (g * torch.sigmoid(g) * u)
+    d = (got.float() - want_own).abs()
+    ulp = 2.0 ** -10 if dtype == mo.FP16 else 2.0 ** -7
+    assert bool((d <= 1.5 * ulp * want_own.abs() + 1e-6).all()), float(d.max())   # fast-math exp / divide: last bit
+    c, _ = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, dtype)
+    want = mo.to_f32(mo.gated_silu_interleaved(c, dtype), dtype).astype(np.float64)
+    st = mo.error_stats(t_load(got, dtype), want, dtype)
+    assert st["max_rel"] <= 2 * TOL_MAX_REL, st     # two T roundings (GEMM, activation) against the oracle's pipeline
+
+
+@pytest.mark.parametrize("m", [1, 16])
+def test_gated_silu_full_size(m):
+    """MiniCPM4-8B gate_up (4096 -> 2 x 16384) with the fused activation, against the activation of the plain output"""
+    b = _b()
+    k, inter = 4096, 16384
+    n = 2 * inter
+    g = torch.Generator(device=DEV).manual_seed(3)
+    qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=DEV, generator=g)
+    sc = (torch.rand((k // 128, n), device=DEV, generator=g) * 0.018 + 0.002).half()
+    a = (torch.randn((m, k), device=DEV, generator=g) * 0.1).half()
+    ws, c_tmp = scratch(m, n, k)
+    plain = b.gemm(a, qw, sc, ws, c_tmp)
+    got = b.gemm(a, qw, sc, ws, c_tmp, gated_silu=True)
+    torch.cuda.synchronize()
+    gg, uu = plain[:, :inter].float(), plain[:, inter:].float()
+    want = gg * torch.sigmoid(gg) * uu
+    d = (got.float() - want).abs()
+    assert bool((d <= 1.5 * 2.0 ** -10 * want.abs() + 1e-6).all()), float(d.max())
+    assert int(ws.abs().max()) == 0
+    with pytest.raises(ValueError):
+        b.gemm(torch.zeros((33, k), dtype=torch.float16, device=DEV), qw, sc, ws, c_tmp, gated_silu=True)
+
+
+@pytest.mark.parametrize("m,k,n", [(64, 16384, 4096), (64, 4096, 32768), (128, 16384, 4096)])
+def test_tcgen05_splitk_repeatable_under_load(m, k, n):
+    """Regression for the co-resident split-K race: with two split-K CTAs of one launch on an SM,
+    about 1.5 % of the launches at M = 64 returned a wrong 16..64-column block.  The launch now keeps one such CTA
+    per SM; every one of 300 back-to-back launches (PDL on, a streaming launch in between) must be bit-identical
+    and within tolerance of the exact result."""
+    b = _b()
+    g = torch.Generator(device=DEV).manual_seed(k + n)
+    qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=DEV, generator=g)
+    sc = (torch.rand((k // 128, n), device=DEV, generator=g) * 0.018 + 0.002).half()
+    a = torch.randn((m, k), device=DEV, generator=g).half()
+    a2 = torch.randn((7, k), device=DEV, generator=g).half()
+    ws, c_tmp = scratch(m, n, k)
+    ref = b.gemm(a, qw, sc, ws, c_tmp).clone()
+    exact = (a.double() @ b.dequant(qw, sc, k, n).double()).cpu().numpy()
+    assert mo.error_stats(ref.cpu().numpy(), exact, mo.FP16)["max_rel"] <= TOL_MAX_REL
+    out = torch.empty_like(ref)
+    bad = 0
+    for i in range(300):
+        if i % 3 == 0:
+            b.gemm(a2, qw, sc, ws, c_tmp)
+        b.gemm(a, qw, sc, ws, c_tmp, out=out, pdl=True)
+        bad += 0 if torch.equal(out, ref) else 1
+    assert bad == 0, f"{bad}/300 launches differ"
+
+
 def test_error_convention():
     b = _b()
     a = torch.zeros((1, 128), dtype=torch.float16, device=DEV)

@@ -1,4 +1,4 @@
-D=gpurun_out/j1
+D=gpurun_out/${1:-j1}
 mkdir -p $D
 timeout 1500 python -m pytest tests -m gpu -q > $D/pytest_gpu.txt 2>&1; tail -n 2 $D/pytest_gpu.txt
 timeout 600 python bench.py --impl reference > $D/bench_reference.json 2> $D/bench_reference.err
