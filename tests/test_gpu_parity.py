@@ -406,6 +406,9 @@ def test_tcgen05_splitk_repeatable_under_load(m, k, n):
     a = torch.randn((m, k), device=DEV, generator=g).half()
     a2 = torch.randn((7, k), device=DEV, generator=g).half()
     ws, c_tmp = scratch(m, n, k)
+    _, c_tmp7 = scratch(7, n, k)      # the streaming launch in between needs its own split-K scratch size
+    if c_tmp7.numel() > c_tmp.numel():
+        c_tmp = c_tmp7
     ref = b.gemm(a, qw, sc, ws, c_tmp).clone()
     exact = (a.double() @ b.dequant(qw, sc, k, n).double()).cpu().numpy()
     assert mo.error_stats(ref.cpu().numpy(), exact, mo.FP16)["max_rel"] <= TOL_MAX_REL
