@@ -10,7 +10,11 @@ import cpmcu_b200 as B
 dev = "cuda"
 iters = int(sys.argv[1]) if len(sys.argv) > 1 else 300
 g = torch.Generator(device=dev).manual_seed(1)
-for (m, k, n) in [(64, 16384, 4096), (64, 4096, 4096), (64, 4096, 32768), (48, 16384, 4096), (128, 16384, 4096), (256, 4096, 4608)]:
+SHAPES = [(64, 16384, 4096), (64, 4096, 4096), (64, 4096, 32768), (48, 16384, 4096), (128, 16384, 4096), (256, 4096, 4608)]
+if len(sys.argv) > 2 and sys.argv[2] == "decode":   # the streaming regime (persistent stream-K kernel, PDL co-residency)
+    SHAPES = [(1, 4096, 4608), (1, 4096, 32768), (1, 16384, 4096), (8, 16384, 4096), (16, 4096, 32768), (16, 16384, 4096),
+              (32, 4096, 4096), (32, 4096, 32768)]
+for (m, k, n) in SHAPES:
     qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=dev, generator=g)
     sc = (torch.rand((k // 128, n), device=dev, generator=g) * 0.018 + 0.002).half()
     a = torch.randn((m, k), device=dev, generator=g).half()
