@@ -45,6 +45,9 @@ struct PrefillCfg {
   static constexpr int S_STAGE = GROUPED ? BN * 2 : 0;
   static constexpr int ACC_COLS = NSUB * BM;       // fp32 TMEM columns per accumulator
   static constexpr int ACC_STAGES = (!SPLIT && (512 / ACC_COLS) >= 2) ? 2 : 1;
+#ifndef B200_TC_LATE_Q_RELEASE
+#define B200_TC_LATE_Q_RELEASE 1  // 0 reproduces the round-1 race
+#endif
 #ifndef B200_TC_SPLIT_TMEM_ALL
 #define B200_TC_SPLIT_TMEM_ALL 0
 #endif
@@ -267,7 +270,9 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
         asm volatile("" ::"r"(q[i].x), "r"(q[i].y), "r"(q[i].z), "r"(q[i].w) : "memory");
       asm volatile("" ::"r"(s_lo[0]), "r"(s_lo[1]), "r"(s_lo[2]), "r"(s_lo[3]) : "memory");
       __syncwarp();
+#if !B200_TC_LATE_Q_RELEASE
       if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);  // raw slot is in registers now
+#endif
 
       mbar_wait(bar_consumed + 8 * s, wph);  // W slot drained by the tensor core
       const uint32_t w_addr = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
@@ -286,6 +291,11 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
         }
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
       __syncwarp();
+#if B200_TC_LATE_Q_RELEASE
+      // the raw slot is released only after its words were USED (the dequantised tile is written): the
+      // shared-memory loads are then complete by data dependence, not by an assumption about issue order
+      if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);
+#endif
       if (lane == 0) mbar_arrive(bar_w_full + 8 * s);
       sq += Cfg::DGROUPS;
       if (sq >= QSTAGES) { sq -= QSTAGES; qph ^= 1u; }

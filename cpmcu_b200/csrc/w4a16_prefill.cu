@@ -33,11 +33,11 @@ int launch_one(const GemmCall& g, int S, int* query) {
   using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
   auto kern = w4a16_prefill_kernel<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
   static bool attr_set = false;  // benign race: idempotent
-  // Split-K tiles run ONE CTA per SM: with two co-resident CTAs (87-110 KB each) and >= 32 k-blocks per CTA about
-  // 1.5 % of the launches at M = 64 returned a wrong 16..64-column block (tools/stress_m64*.py, profiles/r01/k_*;
-  // never seen with one CTA per SM in > 10^4 launches).  Until that race is found the launch asks for more than
-  // half an SM's shared memory, which rules co-residency out.  B200_W4A16_TC_CORESIDENT=1 restores the old launch.
-  static const bool coresident = [] { const char* e = std::getenv("B200_W4A16_TC_CORESIDENT"); return e && e[0] == '1'; }();
+  // Two split-K CTAs (87-110 KB each) share an SM.  Round 1 found 1-2 % wrong launches in exactly that situation:
+  // the dequantisers released a raw int4 slot right after ISSUING its shared-memory loads, and under the heavier
+  // load of two CTAs the TMA refill could land first (fixed in prefill_kernel.cuh: the slot is released after its
+  // words were used).  B200_W4A16_TC_CORESIDENT=0 keeps one CTA per SM (117 KB request) for debugging.
+  static const bool coresident = [] { const char* e = std::getenv("B200_W4A16_TC_CORESIDENT"); return !(e && e[0] == '0'); }();
   // B200_W4A16_TC_PAD: 2 = every split-K launch is padded; 1 = only launches with more CTAs than SMs (CTAs of the
   // SAME launch would share an SM; the next launch's CTAs may still co-reside under PDL); 0 = never
   static const int pad_mode = [] { const char* e = std::getenv("B200_W4A16_TC_PAD"); return e ? std::atoi(e) : 2; }();
@@ -201,7 +201,7 @@ void prefill_pick(const GemmCall& g, int* tile_out, int* S_out) {
     const int tiles = ((n + 127) / 128) * ((m + bm - 1) / bm);
     const int kblks = g.k / 64;
     // one CTA per SM (see launch_one: co-resident split-K CTAs are switched off), one wave when possible
-    static const bool coresident = [] { const char* e = std::getenv("B200_W4A16_TC_CORESIDENT"); return e && e[0] == '1'; }();
+    static const bool coresident = [] { const char* e = std::getenv("B200_W4A16_TC_CORESIDENT"); return !(e && e[0] == '0'); }();
     const int cap = coresident ? (2 * sms * 9) / 10 : sms;
     int s = 8;
     while (s > 1 && (kblks / s < 4 || tiles * s > cap)) s >>= 1;
