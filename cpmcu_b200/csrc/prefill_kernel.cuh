@@ -263,8 +263,10 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
       for (int i = 0; i < Cfg::RPW; ++i)
         q[i] = lds128(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE + q_lane + i * (Cfg::WPC * CHUNKS * 512));
-      // the slot may be overwritten by TMA as soon as it is released: make the release wait for the
-      // LDS results (an arrive has no data dependency on outstanding loads by itself)
+      // The slot may be overwritten by TMA as soon as it is released.  The compile-only barriers below keep the
+      // loads above the (early, B200_TC_LATE_Q_RELEASE == 0) release in program order, but they do NOT make the
+      // hardware wait for the loads: that early release was the round-1 race.  The default
+      // releases the slot after its words were used, further down.
 #pragma unroll
       for (int i = 0; i < Cfg::RPW; ++i)
         asm volatile("" ::"r"(q[i].x), "r"(q[i].y), "r"(q[i].z), "r"(q[i].w) : "memory");

@@ -396,9 +396,9 @@ def test_gated_silu_full_size(m):
 @pytest.mark.parametrize("m,k,n", [(64, 16384, 4096), (64, 4096, 32768), (128, 16384, 4096)])
 def test_tcgen05_splitk_repeatable_under_load(m, k, n):
     """Regression for the co-resident split-K race: with two split-K CTAs of one launch on an SM,
-    about 1.5 % of the launches at M = 64 returned a wrong 16..64-column block.  The launch now keeps one such CTA
-    per SM; every one of 300 back-to-back launches (PDL on, a streaming launch in between) must be bit-identical
-    and within tolerance of the exact result."""
+    about 1.5 % of the launches at M = 64 returned a wrong 16..64-column block (a raw int4 slot was released
+    before its shared-memory loads had completed).  Every one of 300 back-to-back launches (PDL on, a streaming
+    launch in between) must be bit-identical and within tolerance of the exact result."""
     b = _b()
     g = torch.Generator(device=DEV).manual_seed(k + n)
     qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=DEV, generator=g)
