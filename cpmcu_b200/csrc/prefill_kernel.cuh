@@ -272,8 +272,19 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
         asm volatile("" ::"r"(q[i].x), "r"(q[i].y), "r"(q[i].z), "r"(q[i].w) : "memory");
       asm volatile("" ::"r"(s_lo[0]), "r"(s_lo[1]), "r"(s_lo[2]), "r"(s_lo[3]) : "memory");
       __syncwarp();
-#if !B200_TC_LATE_Q_RELEASE
-      if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);  // raw slot is in registers now
+#if B200_TC_LATE_Q_RELEASE == 0
+      if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);  // UNSAFE (the round-1 race): nothing waits for the loads
+#elif B200_TC_LATE_Q_RELEASE == 2
+      {
+        // early release with a TRUE dependency: the arrive's address is computed from every loaded word (masked
+        // with a run-time zero the compiler cannot fold), so the hardware scoreboard holds it until the loads of
+        // this warp have returned; the slot goes back to the TMA producer a whole dequant pass earlier than mode 1
+        uint32_t dep = s_lo[0] ^ s_lo[1] ^ s_lo[2] ^ s_lo[3];
+#pragma unroll
+        for (int i = 0; i < Cfg::RPW; ++i) dep ^= q[i].x ^ q[i].y ^ q[i].z ^ q[i].w;
+        dep &= static_cast<uint32_t>(p.dbg) >> 24;
+        if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq + dep);
+      }
 #endif
 
       mbar_wait(bar_consumed + 8 * s, wph);  // W slot drained by the tensor core
@@ -293,7 +304,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
         }
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
       __syncwarp();
-#if B200_TC_LATE_Q_RELEASE
+#if B200_TC_LATE_Q_RELEASE == 1
       // the raw slot is released only after its words were USED (the dequantised tile is written): the
       // shared-memory loads are then complete by data dependence, not by an assumption about issue order
       if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);
