@@ -18,6 +18,8 @@ from .capi import (  # noqa: F401
     lib,
     library_path,
     reduce_bytes,
+    reduce_bytes_fast,
+    set_scratch_capacity,
     reduce_max_m,
     workspace_ints,
     launch_count,

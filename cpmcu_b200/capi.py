@@ -52,12 +52,17 @@ SYMBOLS = {
     "b200_w4a16_linear_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_int, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p,
                                           c_void_p]),
+    "b200_w4a16_linear_forward_ex": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                             c_int, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p,
+                                             c_int64, c_void_p]),
     "b200_w4a16_dense_linear_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64,
                                                 c_int64, c_float, c_int, c_int, c_void_p]),
     "b200_w4a16_dequant": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p]),
     "b200_w4a16_repack_gptq": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p]),
     "b200_w4a16_reduce_max_m": (c_int, [c_int64]),
     "b200_w4a16_reduce_bytes": (c_int64, [c_int64, c_int64, c_int64]),
+    "b200_w4a16_reduce_bytes_fast": (c_int64, [c_int64, c_int64, c_int64]),
+    "b200_w4a16_set_scratch_capacity": (c_int64, [c_int64]),
     "b200_w4a16_workspace_ints": (c_int64, [c_int64]),
     "b200_w4a16_launch_count": (c_int64, []),
     "b200_w4a16_set_pdl": (c_int, [c_int]),
@@ -126,6 +131,16 @@ def reduce_bytes(m: int, n: int, k: int) -> int:
     return lib().b200_w4a16_reduce_bytes(m, n, k)
 
 
+def reduce_bytes_fast(m: int, n: int, k: int) -> int:
+    """bytes of c_tmp full-width stream-K needs (reduce_bytes: what is touched inside the reference's contract)"""
+    return lib().b200_w4a16_reduce_bytes_fast(m, n, k)
+
+
+def set_scratch_capacity(nbytes: int) -> int:
+    """process-wide promise about every c_tmp passed without a size; returns the previous value"""
+    return lib().b200_w4a16_set_scratch_capacity(nbytes)
+
+
 def workspace_ints(n: int) -> int:
     return lib().b200_w4a16_workspace_ints(n)
 
@@ -153,8 +168,9 @@ def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm
     """C[M,N] = A[M,K] . dequant(qweight, scales)  (+ residual, + bias, * T(out_scale)) on the current stream.
 
     a: [M,K] fp16/bf16 cuda, qweight: int32 [K/16, 2N] cuda (Marlin), scales: [K/g, N] (Marlin-permuted),
-    workspace: int32 [(N/64)*16] zeroed, c_tmp: float32 scratch of >= reduce_bytes(M,N,K) bytes
-    (may be None when reduce_bytes is 0, i.e. on the tcgen05 path, M > 64)."""
+    workspace: int32 [(N/64)*16] zeroed, c_tmp: float32 scratch (its size is passed along: the library uses
+    full-width stream-K when it holds reduce_bytes_fast(M,N,K) bytes and stays inside whatever it is given
+    otherwise; may be None on the tcgen05 path, M > 32)."""
     import torch
     assert a.is_cuda and a.is_contiguous() and qweight.is_contiguous() and scales.is_contiguous()
     m, k = a.shape

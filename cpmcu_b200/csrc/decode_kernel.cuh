@@ -14,16 +14,18 @@
 //                 At the end of a column segment the WK warps sharing a chunk reduce into one fp32 tile
 //                 in shared memory (fixed order), hand it to the flusher through an mbarrier and go
 //                 straight on to the next unit.
-//       flusher   turns finished tiles into output OFF the consumers' critical path.  A column whose K
-//                 range is split over several CTAs is reduced through fp32 slots in c_tmp: the CTAs
-//                 holding later K ranges publish their partial and raise a flag in `workspace`
-//                 (st.release); the CTA holding the column's FIRST k-blocks — always the last segment
-//                 of its own range, so it finishes last — acquires the flags, adds the partials in slot
-//                 order (bit-deterministic), writes T, and resets the flags to zero (the reference's
-//                 workspace contract; the reference serialises the CTAs of a column through a spin
-//                 lock instead, marlin_device_ops.cuh:347-377).
-//   * shared memory <= ~110 KB and <= 56 registers for M <= 8, so that with PDL the NEXT linear's CTA is
-//     co-resident on every SM and has its ring full when this kernel drains.
+//       flusher   turns finished tiles into output OFF the consumers' critical path; the CTA's LAST
+//                 segment is finished by the consumer warps themselves (nothing left to overlap with).
+//   * a column whose K range is split over several CTAs is reduced WITHOUT ANY WAITING: every sharer
+//     writes its fp32 partial to its slot in c_tmp, fences, and takes a ticket from one counter per
+//     column in `workspace` (atomicAdd).  The sharer that draws the LAST ticket knows every other partial
+//     is visible: it adds them IN SLOT ORDER (bit-deterministic, whoever happens to be last), applies the
+//     epilogue, writes T and puts the counter back to zero — the reference's workspace contract
+//     (zero on entry, zero on return; the reference serialises the CTAs of a column through a spin lock
+//     instead, marlin_device_ops.cuh:347-377).  No CTA ever spins on another CTA, so the kernel makes
+//     progress under ANY schedule: partial residency, other streams, MPS — nothing has to be co-resident.
+//   * small CTAs (<= ~110 KB of shared memory, <= 96 registers x 320 threads) so that with PDL the NEXT
+//     linear's CTA is co-resident on every SM and has its ring full when this kernel drains.
 #pragma once
 #include "common.cuh"
 
@@ -32,7 +34,7 @@ namespace b200 {
 struct DecodeArgs {
   void* c;               // T[M][N]
   float* c_tmp;          // split-K slots
-  int32_t* workspace;    // tickets, one per column tile
+  int32_t* workspace;    // one arrival counter per column tile (first int of the tile's FLAGS_PER_TILE)
   const void* scales;    // raw pointer (channelwise epilogue)
   const void* bias;      // T[N] or null
   const void* residual;  // T[M][N] or null
@@ -78,8 +80,11 @@ struct DecodeCfg {
   static constexpr int OFF_S = OFF_W + NSTAGE * W_STAGE;
   static constexpr int OFF_RED = (OFF_S + NSTAGE * S_STAGE + 127) / 128 * 128;
   static constexpr int OFF_BAR = OFF_RED + RED_BYTES;
-  static constexpr int SMEM_BYTES = OFF_BAR + (2 * NSTAGE + 2) * 8 + 16;
+  static constexpr int OFF_TK = OFF_BAR + (2 * NSTAGE + 2) * 8;  // two ticket broadcast words (flusher, consumers)
+  static constexpr int SMEM_BYTES = OFF_TK + 16;
   static constexpr int THREADS = WARPS * 32 + 64;  // + producer warp + flusher warp
+  // two CTAs per SM (PDL co-residency with the next linear) while the register file allows it
+  static constexpr int MINB = (WARPS <= 8 && NT <= 2) ? 2 : 1;
   static constexpr int FLAGS_PER_TILE = CHUNKS * 16;  // ints of `workspace` owned by one column tile
   static_assert(WARPS % CHUNKS == 0 && KROWS % WK == 0, "warp layout");
   static_assert(KB % 64 == 0 && (KB <= 128 || (KB % 128 == 0 && 8 % WK == 0)), "stage k: a multiple of the 128-byte activation row; one group, or whole groups whose 8 k16-rows fall to one row index i of every warp");
@@ -93,15 +98,6 @@ __device__ __forceinline__ int unit_begin(int cta, long long units, int grid) {
 // the CTA whose range contains unit u: largest i with floor(i*U/G) <= u
 __device__ __forceinline__ int cta_of_unit(long long u, long long units, int grid) {
   return static_cast<int>(((u + 1) * grid - 1) / units);
-}
-
-__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
-  int v;
-  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_gpu(int* p, int v) {
-  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 // converts 4 fp32 sums to T with the reference's rounding points (RN to T; channelwise scale on the
@@ -163,7 +159,7 @@ __device__ __forceinline__ void emit_gated(const DecodeArgs& p, int tok, int n_o
 struct ColumnShare {
   int nparts, my_slot;
   float* slots;   // c_tmp slots of this column: [slot][m][TN] fp32
-  int* flags;     // one int per slot in `workspace` (slot 0, the owner's, stays unused)
+  int* counter;   // arrival counter of this column in `workspace`; zero between launches
   size_t slot_elems;
 };
 template <int TN, int FLAGS_PER_TILE>
@@ -176,14 +172,147 @@ __device__ __forceinline__ ColumnShare column_share(const DecodeArgs& p, int c, 
   cs.my_slot = static_cast<int>(blockIdx.x) - cta_first;
   cs.slot_elems = static_cast<size_t>(p.m) * TN;
   cs.slots = p.c_tmp + static_cast<size_t>(c) * p.slot_max * cs.slot_elems;
-  cs.flags = p.workspace + c * FLAGS_PER_TILE;
+  cs.counter = p.workspace + c * FLAGS_PER_TILE;
   return cs;
+}
+
+struct WarpSync {
+  __device__ __forceinline__ void operator()() const { __syncwarp(); }
+};
+template <int NTHR>
+struct ConsumerSync {  // named barrier 1: the consumer warps only
+  __device__ __forceinline__ void operator()() const { named_bar_sync(1, NTHR); }
+};
+
+// Turns the finished fp32 tile `red` ([token][TNP]) of column tile c into output.  Called by a whole thread
+// group (the flusher warp, or all consumer warps for the CTA's last segment) with `tid` in [0, nthr).
+//   whole column                  -> epilogue + store.
+//   split column (nparts sharers) -> publish the partial, fence, take a ticket; the LAST ticket holder adds all
+//                                    partials in slot order, stores, and zeroes the counter.  Nobody waits.
+// `stage` (may be null): `cap` float4 of dead shared memory the last arriver may use to pull the other
+// partials with every copy in flight at once; without it the partials are read straight from L2.
+template <typename T, int TN, int TNP, int FLAGS_PER_TILE, bool GROUPED, bool GATED, typename Sync>
+__device__ __forceinline__ void finish_segment(const DecodeArgs& p, const float* red, int c, bool whole,
+                                               long long units, int grid, int tid, int nthr, Sync sync,
+                                               volatile int* tk, float4* stage, int cap) {
+  constexpr int RI = TN / 4;               // float4 items per token row
+  const int items = p.m * RI;              // float4 items of the valid token rows
+  const int col0 = c * TN;
+  const int gcol0 = c * (TN / 2);          // gated: first output column of the tile
+  auto own_item = [&](int item) {
+    const int tok = item / RI, nn = (item - tok * RI) * 4;
+    return *reinterpret_cast<const float4*>(red + tok * TNP + nn);
+  };
+  if (whole) {
+    if (GATED) {
+      for (int e = tid; e < p.m * (RI / 2); e += nthr) {
+        const int tok = e / (RI / 2), jj = e - tok * (RI / 2);
+        emit_gated<T>(p, tok, gcol0 + jj * 4, own_item(tok * RI + jj), own_item(tok * RI + RI / 2 + jj));
+      }
+    } else {
+      for (int e = tid; e < items; e += nthr) {
+        const int tok = e / RI, nn = (e - tok * RI) * 4;
+        if (col0 + nn < p.n) emit_out<T, GROUPED>(p, tok, col0 + nn, own_item(e));
+      }
+    }
+    return;
+  }
+  const ColumnShare cs = column_share<TN, FLAGS_PER_TILE>(p, c, units, grid);
+  // ---- publish: fp32 partial -> own slot; fence; ticket ----
+  {
+    float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
+    for (int e = tid; e < items; e += nthr) __stcg(reinterpret_cast<float4*>(mine) + e, own_item(e));
+  }
+  __threadfence();   // every writer: its stores are visible device-wide before the ticket below is drawn
+  sync();
+  if (tid == 0) *tk = atomicAdd(cs.counter, 1);
+  sync();
+  if (*tk != cs.nparts - 1) return;   // somebody else arrives later and finishes the column
+  // ---- last arriver: every other partial is visible (their fences precede their tickets) ----
+  __threadfence();
+  if (tid == 0) *cs.counter = 0;      // all sharers have drawn: the workspace goes back to zero (reference contract)
+  const int np1 = cs.nparts - 1;
+  if (stage == nullptr || cap < np1 * (GATED ? RI : 1)) {
+    // straight from L2 (the flusher warp drew the last ticket: rare, its shared memory is live)
+    auto sum_item = [&](int item) {
+      float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int sl = 0; sl < cs.nparts; ++sl) {   // slot order: bit-deterministic
+        const float4 v = (sl == cs.my_slot) ? own_item(item)
+                                            : __ldcg(reinterpret_cast<const float4*>(cs.slots + sl * cs.slot_elems) + item);
+        if (sl == 0) {
+          sum = v;
+        } else {
+          sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+        }
+      }
+      return sum;
+    };
+    if (GATED) {
+      for (int e = tid; e < p.m * (RI / 2); e += nthr) {
+        const int tok = e / (RI / 2), jj = e - tok * (RI / 2);
+        emit_gated<T>(p, tok, gcol0 + jj * 4, sum_item(tok * RI + jj), sum_item(tok * RI + RI / 2 + jj));
+      }
+    } else {
+      for (int e = tid; e < items; e += nthr) {
+        const int tok = e / RI, nn = (e - tok * RI) * 4;
+        if (col0 + nn < p.n) emit_out<T, GROUPED>(p, tok, col0 + nn, sum_item(e));
+      }
+    }
+    return;
+  }
+  // staged: rounds of `ib` items; all copies of a round in flight at once (16-byte cp.async, L2 -> shared).
+  // Whole token rows per round when gated, so that a gate item and its up item are staged together.
+  const int ib = GATED ? (cap / np1) / RI * RI : cap / np1;
+  for (int i0 = 0; i0 < items; i0 += ib) {
+    const int ni = (items - i0) < ib ? (items - i0) : ib;
+    for (int sl = 0, row = 0; sl < cs.nparts; ++sl) {
+      if (sl == cs.my_slot) continue;
+      const float4* src = reinterpret_cast<const float4*>(cs.slots + sl * cs.slot_elems) + i0;
+      const uint32_t dst = smem_u32(stage + row * ni);
+      for (int e = tid; e < ni; e += nthr)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + e * 16), "l"(src + e) : "memory");
+      ++row;
+    }
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+    sync();
+    auto sum_item = [&](int e) {   // e: item index inside the round
+      float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int sl = 0, row = 0; sl < cs.nparts; ++sl) {   // slot order: bit-deterministic
+        float4 v;
+        if (sl == cs.my_slot) {
+          v = own_item(i0 + e);
+        } else {
+          v = stage[row * ni + e];
+          ++row;
+        }
+        if (sl == 0) {
+          sum = v;
+        } else {
+          sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+        }
+      }
+      return sum;
+    };
+    if (GATED) {
+      for (int e = tid; e < ni / 2; e += nthr) {
+        const int r = e / (RI / 2), jj = e - r * (RI / 2);
+        emit_gated<T>(p, i0 / RI + r, gcol0 + jj * 4, sum_item(r * RI + jj), sum_item(r * RI + RI / 2 + jj));
+      }
+    } else {
+      for (int e = tid; e < ni; e += nthr) {
+        const int item = i0 + e;
+        const int tok = item / RI, nn = (item - tok * RI) * 4;
+        if (col0 + nn < p.n) emit_out<T, GROUPED>(p, tok, col0 + nn, sum_item(e));
+      }
+    }
+    sync();
+  }
 }
 
 // GATED: the fused [gate | up] tile + SiLU(gate) * up epilogue; a template parameter (not a runtime flag) so
 // that the plain kernels keep their register allocation and code exactly (a runtime flag cost 2 % at M <= 8)
 template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED, bool GATED = false>
-__global__ void __launch_bounds__(WARPS * 32 + 64, (NT == 1 || (NT == 2 && WARPS <= 8)) ? 2 : 1)  // 2: PDL co-residency
+__global__ void __launch_bounds__(WARPS * 32 + 64, DecodeCfg<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>::MINB)
 w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_s,
                     const __grid_constant__ CUtensorMap tm_a, const DecodeArgs p) {
   using Cfg = DecodeCfg<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>;
@@ -203,6 +332,7 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   const uint32_t bar_empty = bar_full + NS * 8;
   const uint32_t bar_red_full = bar_empty + NS * 8;   // consumers -> flusher: tile complete
   const uint32_t bar_red_empty = bar_red_full + 8;        // flusher -> consumers: tile consumed
+  volatile int* tk = reinterpret_cast<volatile int*>(smem + Cfg::OFF_TK);  // [0] flusher, [1] consumers
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -293,8 +423,8 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
 
   if (warp == WARPS + 1) {
     // ======================================= flusher =======================================
-    // walks the same column segments as the consumers; every global write of the kernel is here
-    pdl_wait_prior_grids();  // C, c_tmp and the flags are shared with prior grids
+    // walks the same column segments as the consumers and finishes all but the CTA's last one
+    pdl_wait_prior_grids();  // C, c_tmp and the counters are shared with prior grids
     int u = u0;
     uint32_t seg = 0;
     while (true) {
@@ -303,34 +433,9 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       const int col_end = (c + 1) * p.kblks;
       const int uend = u1 < col_end ? u1 : col_end;
       if (uend == u1) break;  // the CTA's last segment is finished by the consumer warps themselves
-      const bool whole = (b_first == 0);
       mbar_wait_backoff(bar_red_full, seg & 1u, 64);
-      const int items = p.m * (TN / 4);  // float4 items of the valid token rows
-      const int col0 = c * TN;
-      if (whole && GATED) {
-        for (int e = lane; e < p.m * (TN / 8); e += 32) {
-          const int tok = e / (TN / 8), nn = (e - tok * (TN / 8)) * 4;
-          emit_gated<T>(p, tok, c * (TN / 2) + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn),
-                        *reinterpret_cast<const float4*>(red + tok * TNP + TN / 2 + nn));
-        }
-      } else if (whole) {
-        for (int e = lane; e < items; e += 32) {
-          const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
-          if (col0 + nn < p.n)
-            emit_out<T, GROUPED>(p, tok, col0 + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn));
-        }
-      } else {
-        // an early segment that does not start its column: publish the fp32 partial, raise the flag
-        const ColumnShare cs = column_share<TN, Cfg::FLAGS_PER_TILE>(p, c, units, grid);
-        float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
-        for (int e = lane; e < items; e += 32) {
-          const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
-          __stcg(reinterpret_cast<float4*>(mine + static_cast<size_t>(e) * 4),
-                 *reinterpret_cast<const float4*>(red + tok * TNP + nn));
-        }
-        __syncwarp();  // the release below is cumulative over the stores ordered before it by this barrier
-        if (lane == 0) st_release_gpu(cs.flags + cs.my_slot, 1);
-      }
+      finish_segment<T, TN, TNP, Cfg::FLAGS_PER_TILE, GROUPED, GATED>(p, red, c, /*whole=*/b_first == 0, units, grid,
+                                                                       lane, 32, WarpSync(), tk, nullptr, 0);
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_red_empty);
       u = uend;
@@ -428,7 +533,7 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
     if (lane == 0) mbar_arrive(bar_empty + 8 * s);
     if (++s == NS) { s = 0; ph ^= 1u; }
 
-    // ---- end of this CTA's run inside the column?  hand the tile to the flusher ----
+    // ---- end of this CTA's run inside the column?  hand the tile over ----
     if (b == p.kblks - 1 || it == my_units - 1) {
       mbar_wait(bar_red_empty, (seg & 1u) ^ 1u);  // previous tile consumed (passes the first time)
       // the WK warps sharing a chunk add their partials in wk order (fixed -> deterministic)
@@ -453,216 +558,17 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
         if (r + 1 < WK) named_bar_sync(1, NCONS);
       }
       if (it == my_units - 1) {
-        // last segment of this CTA: nothing left to overlap with -> all consumer warps finish it
+        // last segment of this CTA: nothing left to overlap with -> all consumer warps finish it; the weight
+        // ring is dead by now (every stage consumed) and serves as the staging area of the reduction
         if (threadIdx.x == 0) dbg_stamp1(p, 3);
         named_bar_sync(1, NCONS);
-        pdl_wait_prior_grids();  // C, c_tmp and the flags are shared with prior grids
+        pdl_wait_prior_grids();  // C, c_tmp and the counters are shared with prior grids
         const int c_last = (u1 - 1) / p.kblks;
-        const bool whole = (b == p.kblks - 1) && (u0 <= c_last * p.kblks);  // segment spans the whole column
+        const bool whole = (b == p.kblks - 1) && (u0 <= c_last * p.kblks);  // the segment spans the whole column
         if (threadIdx.x == 0) dbg_stamp1(p, 5);
-        const int tid = static_cast<int>(threadIdx.x);
-        const int items = p.m * (TN / 4);  // float4 items of the valid token rows
-        const int col0 = c_last * TN;
-        const int gcol0 = c_last * (TN / 2);  // gated: first output column of the tile
-        if (whole && GATED) {
-          for (int e = tid; e < p.m * (TN / 8); e += NCONS) {
-            const int tok = e / (TN / 8), nn = (e - tok * (TN / 8)) * 4;
-            emit_gated<T>(p, tok, gcol0 + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn),
-                          *reinterpret_cast<const float4*>(red + tok * TNP + TN / 2 + nn));
-          }
-        } else if (whole) {
-          for (int e = tid; e < items; e += NCONS) {
-            const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
-            if (col0 + nn < p.n)
-              emit_out<T, GROUPED>(p, tok, col0 + nn, *reinterpret_cast<const float4*>(red + tok * TNP + nn));
-          }
-        } else {
-          if (NT == 1) {
-            // few bytes per tile: ONE sharer (the holder of the column's first k-blocks) adds everything;
-            // the others publish and leave
-            const ColumnShare cs = column_share<TN, Cfg::FLAGS_PER_TILE>(p, c_last, units, grid);
-            if (cs.my_slot != 0) {
-              // publisher: fp32 partial -> its c_tmp slot, then st.release of its flag
-              float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
-              for (int e = tid; e < items; e += NCONS) {
-                const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
-                __stcg(reinterpret_cast<float4*>(mine + static_cast<size_t>(e) * 4),
-                       *reinterpret_cast<const float4*>(red + tok * TNP + nn));
-              }
-              named_bar_sync(1, NCONS);  // the release below is cumulative over the stores ordered before it by this barrier
-              if (tid == 0) st_release_gpu(cs.flags + cs.my_slot, 1);
-            } else {
-              // owner: acquire the other flags, pull every partial into the (now dead) weight ring with
-              // all loads in flight at once, add them in slot order, write T, reset the flags
-              const int np1 = cs.nparts - 1;
-              if (tid >= 1 && tid <= np1) {
-                while (ld_acquire_gpu(cs.flags + tid) == 0) {
-                }
-              }
-              // the owner is the only reader of these flags: reset them now (the reference's workspace
-              // contract), so that the stores are in flight while the partials are fetched
-              if (tid >= 1 && tid <= np1) cs.flags[tid] = 0;
-              named_bar_sync(1, NCONS);
-              if (tid == 0) dbg_stamp1(p, 6);
-              float4* stage = reinterpret_cast<float4*>(smem + Cfg::OFF_W);
-              constexpr int CAP = (NS * Cfg::W_STAGE) / 16;
-              // items per round; whole token rows when gated, so that a gate item and its up item (TN/8
-              // items further in the same row) are staged in the same round
-              const int ib = GATED ? (CAP / np1) / (TN / 4) * (TN / 4) : CAP / np1;
-              for (int i0 = 0; i0 < items; i0 += ib) {
-                const int ni = (items - i0) < ib ? (items - i0) : ib;
-                // fire-and-forget 16-byte copies global(L2) -> shared: every partial of the round in flight at once
-                for (int sl = 0; sl < np1; ++sl) {
-                  const float* src = cs.slots + static_cast<size_t>(sl + 1) * cs.slot_elems + static_cast<size_t>(i0) * 4;
-                  const uint32_t dst = smem_u32(stage + sl * ni);
-                  for (int e = tid; e < ni; e += NCONS)
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + e * 16), "l"(src + e * 4) : "memory");
-                }
-                asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
-                named_bar_sync(1, NCONS);
-                auto sum_item = [&](int e) {  // own partial + the staged ones, in slot order
-                  const int item = i0 + e;
-                  const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
-                  float4 sum = *reinterpret_cast<const float4*>(red + tok * TNP + nn);
-                  for (int sl = 0; sl < np1; ++sl) {
-                    const float4 v = stage[sl * ni + e];
-                    sum.x += v.x;
-                    sum.y += v.y;
-                    sum.z += v.z;
-                    sum.w += v.w;
-                  }
-                  return sum;
-                };
-                if (GATED) {
-                  for (int e = tid; e < ni / 2; e += NCONS) {
-                    const int r = e / (TN / 8), jj = e - r * (TN / 8);
-                    const int eg = r * (TN / 4) + jj;
-                    emit_gated<T>(p, i0 / (TN / 4) + r, gcol0 + jj * 4, sum_item(eg), sum_item(eg + TN / 8));
-                  }
-                } else {
-                  for (int e = tid; e < ni; e += NCONS) {
-                    const int item = i0 + e;
-                    const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
-                    if (col0 + nn >= p.n) continue;
-                    emit_out<T, GROUPED>(p, tok, col0 + nn, sum_item(e));
-                  }
-                }
-                named_bar_sync(1, NCONS);
-              }
-            }
-          } else {
-            // A split column, and this is the last segment of this CTA.  Every sharer whose segment is its
-            // last one ("late": all but possibly the sharer holding the column's final k-blocks, which
-            // published early through its flusher) takes an equal slice of the tile: publish the own
-            // partial, acquire everybody's flag, pull the other partials of the slice into the (now dead)
-            // weight ring with all copies in flight at once, add them in slot order, write T.  The late
-            // sharer that finishes last (counter) resets the flags: the workspace goes back to zero.
-            const ColumnShare cs = column_share<TN, Cfg::FLAGS_PER_TILE>(p, c_last, units, grid);
-            const int col_end = (c_last + 1) * p.kblks;
-            const int last_sharer_end = unit_begin(static_cast<int>(blockIdx.x) - cs.my_slot + cs.nparts, units, grid);
-            const int nlate = cs.nparts - (last_sharer_end > col_end ? 1 : 0);
-            int* done = cs.flags + 15;  // flags 0..14 + counter: inside the first 16 ints of the tile, always in bounds
-            {
-              float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
-              for (int e = tid; e < items; e += NCONS) {
-                const int tok = e / (TN / 4), nn = (e - tok * (TN / 4)) * 4;
-                __stcg(reinterpret_cast<float4*>(mine + static_cast<size_t>(e) * 4),
-                       *reinterpret_cast<const float4*>(red + tok * TNP + nn));
-              }
-              named_bar_sync(1, NCONS);  // the release below is cumulative over the stores ordered before it by this barrier
-              if (tid == 0) st_release_gpu(cs.flags + cs.my_slot, 1);
-            }
-            if (tid < cs.nparts && tid != cs.my_slot) {
-              while (ld_acquire_gpu(cs.flags + tid) == 0) {
-              }
-            }
-            named_bar_sync(1, NCONS);
-            if (tid == 0) dbg_stamp1(p, 6);
-            // measured on B200 (profiles/r01/i_*): counting early wins 2.6 % of a 32-layer pass at M = 32 and
-            // loses 1.5 % at M = 16 (the extra predicate sits in the shorter fetch loop)
-            constexpr bool EARLY_COUNT = NT >= 4;
-            bool counted = false;
-            int prev_count = -1;
-            {
-              // this sharer's slice of the tile: an even share of the items; of the token ROWS when gated,
-              // so that a gate item and its up item (same row) fall to the same sharer and round
-              const int e_lo = GATED ? (cs.my_slot * p.m / nlate) * (TN / 4)
-                                       : static_cast<int>((static_cast<long long>(cs.my_slot) * items) / nlate);
-              const int e_hi = GATED ? ((cs.my_slot + 1) * p.m / nlate) * (TN / 4)
-                                       : static_cast<int>((static_cast<long long>(cs.my_slot + 1) * items) / nlate);
-              const int np1 = cs.nparts - 1;
-              float4* stage = reinterpret_cast<float4*>(smem + Cfg::OFF_W);
-              constexpr int CAP = (NS * Cfg::W_STAGE) / 16;
-              const int ib = GATED ? (CAP / np1) / (TN / 4) * (TN / 4) : CAP / np1;  // items per round
-              for (int i0 = e_lo; i0 < e_hi; i0 += ib) {
-                const int ni = (e_hi - i0) < ib ? (e_hi - i0) : ib;
-                // fire-and-forget 16-byte copies global(L2) -> shared, the own slot skipped
-                for (int sl = 0, row = 0; sl < cs.nparts; ++sl) {
-                  if (sl == cs.my_slot) continue;
-                  const float* src = cs.slots + static_cast<size_t>(sl) * cs.slot_elems + static_cast<size_t>(i0) * 4;
-                  const uint32_t dst = smem_u32(stage + row * ni);
-                  for (int e = tid; e < ni; e += NCONS)
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + e * 16), "l"(src + e * 4) : "memory");
-                  ++row;
-                }
-                asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
-                named_bar_sync(1, NCONS);
-                if (EARLY_COUNT && tid == 0 && i0 + ib >= e_hi) {
-                  // last round landed: this CTA has read every flag and every partial it needs.  Count it
-                  // now, so that the atomic's round trip overlaps the sums below.
-                  counted = true;
-                  prev_count = atomicAdd(done, 1);  // the returned count is looked at after the sums are written
-                }
-                auto sum_item = [&](int e) {
-                  const int item = i0 + e;
-                  const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
-                  const float4 own = *reinterpret_cast<const float4*>(red + tok * TNP + nn);
-                  float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
-                  for (int sl = 0, row = 0; sl < cs.nparts; ++sl) {  // slot order: bit-deterministic
-                    float4 v;
-                    if (sl == cs.my_slot) {
-                      v = own;
-                    } else {
-                      v = stage[row * ni + e];
-                      ++row;
-                    }
-                    if (sl == 0) {
-                      sum = v;
-                    } else {
-                      sum.x += v.x;
-                      sum.y += v.y;
-                      sum.z += v.z;
-                      sum.w += v.w;
-                    }
-                  }
-                  return sum;
-                };
-                if (GATED) {
-                  for (int e = tid; e < ni / 2; e += NCONS) {
-                    const int r = e / (TN / 8), jj = e - r * (TN / 8);
-                    const int eg = r * (TN / 4) + jj;
-                    emit_gated<T>(p, i0 / (TN / 4) + r, gcol0 + jj * 4, sum_item(eg), sum_item(eg + TN / 8));
-                  }
-                } else {
-                  for (int e = tid; e < ni; e += NCONS) {
-                    const int item = i0 + e;
-                    const int tok = item / (TN / 4), nn = (item - tok * (TN / 4)) * 4;
-                    if (col0 + nn >= p.n) continue;
-                    emit_out<T, GROUPED>(p, tok, col0 + nn, sum_item(e));
-                  }
-                }
-                named_bar_sync(1, NCONS);
-              }
-            }
-            if (tid == 0) {
-              if (!counted) prev_count = atomicAdd(done, 1);  // empty slice: nothing was fetched
-              if (prev_count == nlate - 1) {  // every late sharer has read the flags and the partials
-                for (int sl = 0; sl < cs.nparts; ++sl) cs.flags[sl] = 0;
-                *done = 0;  // leave the workspace zeroed (reference contract)
-              }
-            }
-          }
-        }
+        finish_segment<T, TN, TNP, Cfg::FLAGS_PER_TILE, GROUPED, GATED>(
+            p, red, c_last, whole, units, grid, static_cast<int>(threadIdx.x), NCONS, ConsumerSync<NCONS>(), tk + 1,
+            reinterpret_cast<float4*>(smem + Cfg::OFF_W), (NS * Cfg::W_STAGE) / 16);
         if (threadIdx.x == 0) dbg_stamp1(p, 7);
       } else {
         __syncwarp();

@@ -31,7 +31,6 @@ struct PrefillArgs {
   uint32_t out_scale;    // 0, or 0x10000 | bits of T(scale): last post-op
   int m, n, k;
   int n_tiles, m_tiles, kblks;
-  int dbg;  // tuning only: bit0 = dequantisers skip the conversion, bit1 = MMA issuer skips the MMAs
 };
 
 template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT = false>
@@ -45,15 +44,7 @@ struct PrefillCfg {
   static constexpr int S_STAGE = GROUPED ? BN * 2 : 0;
   static constexpr int ACC_COLS = NSUB * BM;       // fp32 TMEM columns per accumulator
   static constexpr int ACC_STAGES = (!SPLIT && (512 / ACC_COLS) >= 2) ? 2 : 1;
-#ifndef B200_TC_LATE_Q_RELEASE
-#define B200_TC_LATE_Q_RELEASE 1  // 0 reproduces the round-1 race
-#endif
-#ifndef B200_TC_SPLIT_TMEM_ALL
-#define B200_TC_SPLIT_TMEM_ALL 0
-#endif
-  // a power of two >= 32 (experiment B200_TC_SPLIT_TMEM_ALL: the split-K tiles take the whole tensor memory,
-  // so that two co-resident CTAs serialise on the allocation)
-  static constexpr int TMEM_COLS = (SPLIT && B200_TC_SPLIT_TMEM_ALL) ? 512 : ACC_COLS * ACC_STAGES;
+  static constexpr int TMEM_COLS = ACC_COLS * ACC_STAGES;  // a power of two >= 32
   // split-K: fp32 partial tile [BM tokens][128 + 4] staged for the cluster reduction; it aliases the
   // A/W rings, which are dead once the last MMA of the CTA's only tile has been committed
   static constexpr int RED_PITCH = 128 + 4;
@@ -217,7 +208,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
             for (int kk = 0; kk < 4; ++kk) {
               const uint64_t adesc = umma_desc_k_sw128(w_addr + sub * 16384 + kk * 32);
               const uint64_t bdesc = umma_desc_k_sw128(a_addr + kk * 32);
-              if (!(p.dbg & 2)) tc_mma_f16(d0 + sub * BM, adesc, bdesc, idesc, (kb != kb_lo || kk != 0) ? 1u : 0u);
+              tc_mma_f16(d0 + sub * BM, adesc, bdesc, idesc, (kb != kb_lo || kk != 0) ? 1u : 0u);
             }
           }
           tc_commit(bar_consumed + 8 * s);
@@ -263,33 +254,8 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
       for (int i = 0; i < Cfg::RPW; ++i)
         q[i] = lds128(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE + q_lane + i * (Cfg::WPC * CHUNKS * 512));
-      // The slot may be overwritten by TMA as soon as it is released.  The compile-only barriers below keep the
-      // loads above the (early, B200_TC_LATE_Q_RELEASE == 0) release in program order, but they do NOT make the
-      // hardware wait for the loads: that early release was the round-1 race.  The default
-      // releases the slot after its words were used, further down.
-#pragma unroll
-      for (int i = 0; i < Cfg::RPW; ++i)
-        asm volatile("" ::"r"(q[i].x), "r"(q[i].y), "r"(q[i].z), "r"(q[i].w) : "memory");
-      asm volatile("" ::"r"(s_lo[0]), "r"(s_lo[1]), "r"(s_lo[2]), "r"(s_lo[3]) : "memory");
-      __syncwarp();
-#if B200_TC_LATE_Q_RELEASE == 0
-      if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);  // UNSAFE (the round-1 race): nothing waits for the loads
-#elif B200_TC_LATE_Q_RELEASE == 2
-      {
-        // early release with a TRUE dependency: the arrive's address is computed from every loaded word (masked
-        // with a run-time zero the compiler cannot fold), so the hardware scoreboard holds it until the loads of
-        // this warp have returned; the slot goes back to the TMA producer a whole dequant pass earlier than mode 1
-        uint32_t dep = s_lo[0] ^ s_lo[1] ^ s_lo[2] ^ s_lo[3];
-#pragma unroll
-        for (int i = 0; i < Cfg::RPW; ++i) dep ^= q[i].x ^ q[i].y ^ q[i].z ^ q[i].w;
-        dep &= static_cast<uint32_t>(p.dbg) >> 24;
-        if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq + dep);
-      }
-#endif
-
       mbar_wait(bar_consumed + 8 * s, wph);  // W slot drained by the tensor core
       const uint32_t w_addr = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
-      if (!(p.dbg & 1))
 #pragma unroll
         for (int i = 0; i < Cfg::RPW; ++i) {
           const uint32_t qq[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
@@ -304,11 +270,10 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
         }
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async proxy
       __syncwarp();
-#if B200_TC_LATE_Q_RELEASE == 1
       // the raw slot is released only after its words were USED (the dequantised tile is written): the
       // shared-memory loads are then complete by data dependence, not by an assumption about issue order
+      // (releasing right after ISSUING the loads was the round-1 split-K race)
       if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);
-#endif
       if (lane == 0) mbar_arrive(bar_w_full + 8 * s);
       sq += Cfg::DGROUPS;
       if (sq >= QSTAGES) { sq -= QSTAGES; qph ^= 1u; }

@@ -18,7 +18,6 @@
 #include <unordered_map>
 
 #include "aux_kernels.cuh"
-#include "decode_kernel.cuh"
 #include "host_common.h"
 
 namespace b200 {
@@ -30,38 +29,20 @@ std::atomic<int> g_default_pdl{[] {
   return (e && e[0] == '1') ? 1 : 0;
 }()};
 
-// which streaming kernel serves M <= 32 by default: 0 = persistent stream-K (decode_kernel.cuh),
-// 1 = cluster split-K (stream_kernel.cuh); environment B200_W4A16_STREAM_V2 overrides
-bool g_stream_v2 = [] {
-  const char* e = std::getenv("B200_W4A16_STREAM_V2");
-  return e ? (e[0] == '1') : false;
-}();
+// Scratch capacity the caller guarantees for every c_tmp passed WITHOUT a size (b200_w4a16_gemm,
+// b200_w4a16_linear_forward, the gptq_marlin_gemm shim): 0 = only the reference contract,
+// determine_reduce_max_m(M, 16) x N floats (gptq_marlin_utils.cu:206-225).  b200_w4a16_set_scratch_capacity.
+std::atomic<long long> g_scratch_capacity{0};
 
-// Per-shape mix of the two streaming kernels (B200_W4A16_STREAM_V2 unset): the cluster split-K kernel
-// reduces through DSMEM (about 1 us) where the persistent stream-K kernel ends in a cross-CTA reduction
-// through L2 (2.5-4 us), so it wins while a launch streams few bytes; the persistent kernel wins on the
-// big shapes (no wave quantisation).  Thresholds in int4 weight bytes (K*N/2) for M <= 8 / 9..16 / 17..32,
-// from the B200 measurements in profiles/r01 (b_bench_ours_stream_v2.json against g_bench_ours_final.json
-// and the i_* mixed-chain runs); 0 = never.
-long long g_mix_bytes[3] = {
-    [] { const char* e = std::getenv("B200_W4A16_MIX_BYTES_M8"); return e ? std::atoll(e) : 0ll; }(),
-    [] { const char* e = std::getenv("B200_W4A16_MIX_BYTES_M16"); return e ? std::atoll(e) : 0ll; }(),
-    [] { const char* e = std::getenv("B200_W4A16_MIX_BYTES_M32"); return e ? std::atoll(e) : 0ll; }(),
-};
-bool g_stream_v2_forced = std::getenv("B200_W4A16_STREAM_V2") != nullptr;
-bool use_cluster_streamer(int mm, long long n, long long k) {
-  if (g_stream_v2_forced) return g_stream_v2;
-  const long long bytes = n * k / 2;
-  const long long thr = g_mix_bytes[mm <= 8 ? 0 : (mm <= 16 ? 1 : 2)];
-  return bytes <= thr;
+// tuning aid: per-launch timestamp blocks (b200_w4a16_debug_timeline)
+unsigned long long* g_dbg_ts = nullptr;
+long long g_dbg_ts_launches = 0;
+std::atomic<long long> g_dbg_ts_next{0};
+unsigned long long* debug_next_slot() {
+  if (!g_dbg_ts) return nullptr;
+  const long long idx = g_dbg_ts_next.fetch_add(1, std::memory_order_relaxed);
+  return idx < g_dbg_ts_launches ? g_dbg_ts + idx * 8192 : nullptr;
 }
-
-// cap on resident CTAs per SM of the first-generation persistent streaming kernel
-int g_v1_occ = [] {
-  const char* e = std::getenv("B200_W4A16_V1_OCC");
-  const int v = e ? std::atoi(e) : 1;
-  return v < 1 ? 1 : (v > 4 ? 4 : v);
-}();
 
 uint32_t out_scale_bits(float v, int dtype) {
   if (v == 0.0f) return 0u;
@@ -187,207 +168,10 @@ int get_tensor_map(CUtensorMap* out, const void* ptr, CUtensorMapDataType type, 
 }
 
 // ------------------------------------------------------------------------------------------
-// decode-regime configurations
+// streaming (decode) regime: launch plan
 // ------------------------------------------------------------------------------------------
-struct DecodeConfig {
-  const char* name;
-  int nt, chunks, krows, warps, stages;
-  bool grouped;
-  int dtype;
-  int (*launch)(const GemmCall&);
-  int smem;
-};
-
-template <typename T, int NT, int CHUNKS, int KROWS, int WARPS, int STAGES, bool GROUPED, bool GATED = false>
-int launch_decode(const GemmCall& g) {
-  using Cfg = DecodeCfg<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED>;
-  auto kern = w4a16_decode_kernel<T, NT, CHUNKS, KROWS, WARPS, STAGES, GROUPED, GATED>;
-  if (g.gated != GATED) return fail(B200_W4A16_ERUNTIME, "internal: gated launch through a plain kernel");
-  static bool attr_set = false;  // benign race: idempotent
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess)
-      return fail(B200_W4A16_ECUDA, "cudaFuncSetAttribute(smem=%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
-    attr_set = true;
-  }
-  CUtensorMap tm_w, tm_s, tm_a;
-  if (g.gated) {
-    // fused gate_up: the tile's first CHUNKS/2 chunks come from the gate half [0, I), the others from the
-    // same columns of the up half [I, 2I) — ONE 4-d box over the views int32 [K/16][2][I/64][128] and
-    // T [K/128][2][I/64][64]; the bytes land exactly where the 3-d box of CHUNKS chunks would put them
-    if ((CHUNKS & 1) || (g.n / 2) % (Cfg::TN / 2) != 0 || !GROUPED)
-      return fail(B200_W4A16_EINVAL, "gated_silu needs group_size 128 and N/2 a multiple of %d, got N = %d", Cfg::TN / 2, g.n);
-    const uint64_t ich = static_cast<uint64_t>(g.n / 2 / 64);
-    {
-      const uint64_t dims[4] = {128, ich, 2, static_cast<uint64_t>(g.k / 16)};
-      const uint64_t strides[3] = {512, ich * 512, static_cast<uint64_t>(g.n) * 8};
-      const uint32_t box[4] = {128, CHUNKS / 2, 2, KROWS};
-      if (int rc = get_tensor_map(&tm_w, g.qweight, CU_TENSOR_MAP_DATA_TYPE_INT32, 4, dims, strides, box,
-                                  CU_TENSOR_MAP_SWIZZLE_NONE))
-        return rc;
-    }
-    {
-      const uint64_t dims[4] = {64, ich, 2, static_cast<uint64_t>(g.k / 128)};
-      const uint64_t strides[3] = {128, ich * 128, static_cast<uint64_t>(g.n) * 2};
-      const uint32_t box[4] = {64, CHUNKS / 2, 2, static_cast<uint32_t>(Cfg::SG)};
-      if (int rc = get_tensor_map(&tm_s, g.scales, Elem<T>::kTmaType, 4, dims, strides, box,
-                                  CU_TENSOR_MAP_SWIZZLE_NONE))
-        return rc;
-    }
-  } else {
-  {  // weights: int32 [K/16][N/64][128]
-    const uint64_t dims[3] = {128, static_cast<uint64_t>(g.n / 64), static_cast<uint64_t>(g.k / 16)};
-    const uint64_t strides[2] = {512, static_cast<uint64_t>(g.n) * 8};
-    const uint32_t box[3] = {128, CHUNKS, KROWS};
-    if (int rc = get_tensor_map(&tm_w, g.qweight, CU_TENSOR_MAP_DATA_TYPE_INT32, 3, dims, strides, box,
-                                CU_TENSOR_MAP_SWIZZLE_NONE))
-      return rc;
-  }
-  if (GROUPED) {  // scales: T [K/128][N/64][64]
-    const uint64_t dims[3] = {64, static_cast<uint64_t>(g.n / 64), static_cast<uint64_t>(g.k / 128)};
-    const uint64_t strides[2] = {128, static_cast<uint64_t>(g.n) * 2};
-    const uint32_t box[3] = {64, CHUNKS, static_cast<uint32_t>(Cfg::SG)};
-    if (int rc = get_tensor_map(&tm_s, g.scales, Elem<T>::kTmaType, 3, dims, strides, box,
-                                CU_TENSOR_MAP_SWIZZLE_NONE))
-      return rc;
-  } else {
-    tm_s = tm_w;
-  }
-  }
-  {  // activations: T [M][K], 64-wide (128-byte) boxes, 128B swizzle, rows past M zero-filled
-    const uint64_t dims[2] = {static_cast<uint64_t>(g.k), static_cast<uint64_t>(g.m)};
-    const uint64_t strides[1] = {static_cast<uint64_t>(g.k) * 2};
-    const uint32_t box[2] = {64, NT * 8};
-    if (int rc = get_tensor_map(&tm_a, g.a, Elem<T>::kTmaType, 2, dims, strides, box,
-                                CU_TENSOR_MAP_SWIZZLE_128B))
-      return rc;
-  }
-  DecodeArgs args;
-  args.gated = g.gated ? 1 : 0;
-  args.c = g.c;
-  args.c_tmp = g.c_tmp;
-  args.workspace = g.workspace;
-  args.scales = g.scales;
-  args.bias = g.bias;
-  args.residual = g.residual;
-  args.out_scale = out_scale_bits(g.out_scale, g.dtype);
-  args.m = g.m;
-  args.n = g.n;
-  args.k = g.k;
-  args.ncols = g.gated ? (g.n / 2) / (Cfg::TN / 2) : (g.n + Cfg::TN - 1) / Cfg::TN;
-  args.kblks = g.k / Cfg::KB;
-  const long long units = static_cast<long long>(args.ncols) * args.kblks;
-  // persistent CTAs: one per SM (B200_W4A16_V1_OCC raises it for experiments, if resources allow)
-  static int occ = 0;
-  if (occ == 0) {
-    int o = 1;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, Cfg::THREADS, Cfg::SMEM_BYTES) != cudaSuccess || o < 1) o = 1;
-    occ = o < g_v1_occ ? o : g_v1_occ;
-  }
-  const long long slots = static_cast<long long>(sm_count()) * occ;
-  int grid = static_cast<int>(units < slots ? units : slots);
-  // column-parallel geometry: CTAs take whole 64-column tiles (no split column, hence no cross-CTA
-  // reduction tail); some SMs idle when there are fewer tiles than SMs
-  args.colpar = (CHUNKS == 1 && KROWS >= 32) ? 1 : 0;
-  if (args.colpar) {
-    grid = static_cast<int>(args.ncols < slots ? args.ncols : slots);
-    args.slot_max = 1;
-  } else {
-    // a column may be shared by at most 15 CTAs (16 ints of `workspace` per 64 columns: one flag per
-    // sharer + the completion counter)
-    while (grid > 1 && decode_slot_max(args.kblks, units, grid) > 15) --grid;
-    args.slot_max = decode_slot_max(args.kblks, units, grid);
-  }
-  args.dbg_ts = stream_debug_next_slot();
-
-  cudaLaunchConfig_t cfg;
-  std::memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(Cfg::THREADS);
-  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
-  cfg.stream = g.stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = g.pdl ? 1 : 0;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tm_w, tm_s, tm_a, args);
-  if (e != cudaSuccess) return fail(B200_W4A16_ECUDA, "decode kernel launch: %s", cudaGetErrorString(e));
-  g_launches.fetch_add(1, std::memory_order_relaxed);
-  return 0;
-}
-
-#define DCFG(T, DT, NT, CH, KR, WP, ST, GR)                                              \
-  {#T "/nt" #NT "/tn" #CH "x64/kb" #KR "x16/w" #WP "/s" #ST "/" #GR, NT, CH, KR, WP, ST, GR, DT, \
-   &launch_decode<T, NT, CH, KR, WP, ST, GR>, DecodeCfg<T, NT, CH, KR, WP, ST, GR>::SMEM_BYTES}
-
-// geometry families (id within family = index):  chunks, krows, warps, stages
-#define DECODE_FAMILY(T, DT, NT, GR)                                                    \
-  DCFG(T, DT, NT, 2, 8, 8, 8, GR), DCFG(T, DT, NT, 4, 8, 8, 5, GR), DCFG(T, DT, NT, 4, 4, 8, 8, GR), \
-      DCFG(T, DT, NT, 8, 4, 8, 5, GR), DCFG(T, DT, NT, 4, 8, 16, 5, GR), DCFG(T, DT, NT, 2, 8, 16, 8, GR), \
-      DCFG(T, DT, NT, 2, 16, 8, 5, GR), DCFG(T, DT, NT, 1, 16, 4, 8, GR), DCFG(T, DT, NT, 3, 16, 12, 3, GR), \
-      DCFG(T, DT, NT, 1, 32, 8, 4, GR)
-constexpr int kGeoms = 10;
-constexpr int kColparGeom = 9;  // 64-column x 512-k stages, launched column-parallel (see launch_decode)
-
-const DecodeConfig g_decode[] = {
-    DECODE_FAMILY(__half, 0, 1, true),          DECODE_FAMILY(__half, 0, 2, true),
-    DECODE_FAMILY(__half, 0, 4, true),          DECODE_FAMILY(__nv_bfloat16, 1, 1, true),
-    DECODE_FAMILY(__nv_bfloat16, 1, 2, true),   DECODE_FAMILY(__nv_bfloat16, 1, 4, true),
-    DECODE_FAMILY(__half, 0, 1, false),         DECODE_FAMILY(__half, 0, 2, false),
-    DECODE_FAMILY(__half, 0, 4, false),         DECODE_FAMILY(__nv_bfloat16, 1, 1, false),
-    DECODE_FAMILY(__nv_bfloat16, 1, 2, false),  DECODE_FAMILY(__nv_bfloat16, 1, 4, false),
-};
-
-// fused gate_up + SiLU(gate) * up: the two default geometries (pick_geometry) of every token-block width
-template <typename T>
-int launch_gated_t(const GemmCall& g, int nt, int geom) {
-  if (geom == 1) {
-    if (nt == 1) return launch_decode<T, 1, 4, 8, 8, 5, true, true>(g);
-    if (nt == 2) return launch_decode<T, 2, 4, 8, 8, 5, true, true>(g);
-    return launch_decode<T, 4, 4, 8, 8, 5, true, true>(g);
-  }
-  if (nt == 1) return launch_decode<T, 1, 4, 4, 8, 8, true, true>(g);
-  if (nt == 2) return launch_decode<T, 2, 4, 4, 8, 8, true, true>(g);
-  return launch_decode<T, 4, 4, 4, 8, 8, true, true>(g);
-}
-int launch_gated(const GemmCall& g, int nt, int geom) {
-  if (geom != 1 && geom != 2) return fail(B200_W4A16_EINVAL, "gated_silu: unsupported geometry %d", geom);
-  return g.dtype == 0 ? launch_gated_t<__half>(g, nt, geom) : launch_gated_t<__nv_bfloat16>(g, nt, geom);
-}
-
-// index into g_decode
-int decode_index(int dtype, int nt, bool grouped, int geom) {
-  const int nti = nt == 1 ? 0 : (nt == 2 ? 1 : 2);
-  return ((grouped ? 0 : 6) + dtype * 3 + nti) * kGeoms + geom;
-}
-
 int nt_for_m(int m) { return m <= 8 ? 1 : (m <= 16 ? 2 : 4); }
 
-// shape -> geometry of the persistent streaming kernel.  Measured on B200 (profiles/r01): the 256-column
-// x 128-k stage with 8 consumer warps (4 k16-rows per warp and stage) has the fewest instructions per
-// byte and leaves room for the next kernel's CTA on the same SM (PDL); stream-K balances any shape.
-int pick_geometry(int m, int n, int k) {
-  // column-parallel (no split column) against stream-K: an SM streams about 29 bytes/ns of int4 at
-  // M <= 8 (24 at M <= 16, 17 beyond; in-loop rates of profiles/r01 g_timeline); stream-K keeps every SM
-  // busy but ends in the cross-CTA reduction of the split columns (about 3.5 us at M <= 8, 5 us beyond)
-  static const int colpar_mode = [] { const char* e = std::getenv("B200_W4A16_COLPAR"); return e ? std::atoi(e) : 0; }();
-  if ((k % 512) == 0 && colpar_mode != 0) {
-    const double rate = m <= 8 ? 29e3 : (m <= 16 ? 24e3 : 17e3);  // bytes per us and SM
-    const double tail = m <= 8 ? 3.5 : 5.0;
-    const double col_bytes = 32.0 * k, cols = n / 64.0;
-    const int sms = sm_count();
-    const double t_colpar = std::ceil(cols / sms) * col_bytes / rate;
-    const double t_streamk = cols * col_bytes / (rate * sms) + tail;
-    if (colpar_mode == 1 || t_colpar < t_streamk) return kColparGeom;
-  }
-  return (k % 128) == 0 ? 1 : 2;  // tn256/kb128/w8, or tn256/kb64/w8 when K is only a multiple of 64
-}
-
-// configuration ids: 1..count = streaming-kernel configurations, kPrefillBase.. = tcgen05 tile shapes
-constexpr int kPrefillBase = 1001;
-// cluster split-K streaming kernel: id = kStreamBase + geometry * 8 + (cluster size - 1)
-constexpr int kStreamBase = 2001;
 // largest M served by the streaming kernel; above it the tcgen05 kernel runs (split-K clusters up to
 // M = 256, persistent whole-K tiles beyond).  Measured crossover on B200: profiles/r01 sweep_mid.
 int kStreamMaxM = [] {
@@ -395,6 +179,117 @@ int kStreamMaxM = [] {
   const int v = e ? std::atoi(e) : 32;
   return v < 0 ? 0 : v;
 }();
+
+int reduce_max_m(long long m) {
+  // mirror of marlin::determine_reduce_max_m(prob_m, max_par = 16), gptq_marlin_utils.cu:206-225
+  if (m <= 16) return 16;
+  if (m <= 32) return 32;
+  if (m <= 48) return 48;
+  if (m <= 64) return 64;
+  long long par = (m + 63) / 64;
+  if (par > 16) par = 16;
+  return static_cast<int>(64 * par);
+}
+
+bool geom_fits(int geo, int n, int k, bool gated) {
+  const int tn = kGeom[geo].chunks * 64, kb = kGeom[geo].krows * 16;
+  if (k % kb) return false;
+  if (gated && (geo > 1 || (n / 2) % (tn / 2) != 0)) return false;
+  return true;
+}
+
+// One slab of mm <= 32 tokens.  `capacity` = bytes of c_tmp the caller guarantees.  Stream-K (every SM
+// streams the same number of bytes; split columns are reduced through fp32 slots in c_tmp) whenever the
+// slots fit; otherwise fewer CTAs (fewer sharers per column) or whole columns per CTA (no scratch at all),
+// whichever leaves the shorter critical path.  geom < 0: the default geometry for the shape.
+DecodePlan plan_decode(int mm, int n, int k, int geom, long long capacity, bool gated) {
+  const int sms = sm_count();
+  auto dims = [&](int geo, DecodePlan* pl) {
+    const int tn = kGeom[geo].chunks * 64, kb = kGeom[geo].krows * 16;
+    pl->geom = geo;
+    pl->ncols = gated ? (n / 2) / (tn / 2) : (n + tn - 1) / tn;
+    pl->kblks = k / kb;
+  };
+  // critical path in bytes of int4 stream: the busiest CTA's units
+  auto path_bytes = [&](const DecodePlan& pl) {
+    const long long unit_bytes = static_cast<long long>(kGeom[pl.geom].chunks) * kGeom[pl.geom].krows * 512;
+    const long long units = static_cast<long long>(pl.ncols) * pl.kblks;
+    const long long per = pl.colpar ? static_cast<long long>((pl.ncols + pl.grid - 1) / pl.grid) * pl.kblks
+                                    : (units + pl.grid - 1) / pl.grid;
+    return per * unit_bytes;
+  };
+  auto full_grid = [&](const DecodePlan& pl) {
+    const long long units = static_cast<long long>(pl.ncols) * pl.kblks;
+    return static_cast<int>(units < sms ? units : sms);
+  };
+  auto stream_k = [&](int geo, DecodePlan* pl) {   // false: not even two slots per column fit
+    dims(geo, pl);
+    const int tn = kGeom[geo].chunks * 64;
+    const long long units = static_cast<long long>(pl->ncols) * pl->kblks;
+    const long long slot_bytes = static_cast<long long>(pl->ncols) * mm * tn * 4;
+    const long long cap = capacity / slot_bytes;
+    pl->colpar = 0;
+    pl->grid = full_grid(*pl);
+    if (pl->kblks == 1) {  // a column is one unit: never shared
+      pl->slot_max = 1;
+      pl->need_bytes = 0;
+      return true;
+    }
+    if (cap < 2) return false;
+    while (pl->grid > 1 && decode_slot_max(pl->kblks, units, pl->grid) > cap) --pl->grid;
+    pl->slot_max = decode_slot_max(pl->kblks, units, pl->grid);
+    if (pl->slot_max > cap) return false;
+    pl->need_bytes = slot_bytes * pl->slot_max;
+    return true;
+  };
+  auto whole_cols = [&](int geo, DecodePlan* pl) {
+    dims(geo, pl);
+    pl->colpar = 1;
+    pl->grid = pl->ncols < sms ? pl->ncols : sms;
+    pl->slot_max = 1;
+    pl->need_bytes = 0;
+  };
+  const int g0 = geom >= 0 ? geom : ((k % 128) == 0 ? 0 : 1);
+  DecodePlan best;
+  bool have = stream_k(g0, &best);
+  if (have && best.grid == full_grid(best)) return best;
+  // scratch too small for full-width stream-K: compare the shrunken grid with whole-column launches
+  DecodePlan alt;
+  whole_cols(g0, &alt);
+  if (!have || path_bytes(alt) < path_bytes(best)) best = alt;
+  if (geom < 0 && !gated && geom_fits(kWholeColGeom, n, k, gated)) {
+    whole_cols(kWholeColGeom, &alt);
+    if (path_bytes(alt) < path_bytes(best)) best = alt;
+  }
+  return best;
+}
+
+// configuration ids (force_config / pick_config): 1 + ((grouped ? 0 : 6) + dtype * 3 + nti) * kGeoms + geom for the
+// streaming kernel, kPrefillBase.. for the tcgen05 tile shapes
+constexpr int kDecodeIds = 12 * kGeoms;
+int decode_id(int dtype, int nt, bool grouped, int geom) {
+  const int nti = nt == 1 ? 0 : (nt == 2 ? 1 : 2);
+  return 1 + ((grouped ? 0 : 6) + dtype * 3 + nti) * kGeoms + geom;
+}
+void decode_from_id(int id, int* dtype, int* nt, bool* grouped, int* geom) {
+  const int r = id - 1;
+  *geom = r % kGeoms;
+  const int fam = r / kGeoms;
+  *grouped = fam < 6;
+  *dtype = (fam % 6) / 3;
+  *nt = 1 << (fam % 3);
+}
+const char* decode_name(int id) {
+  static thread_local char buf[128];
+  int dtype, nt, geom;
+  bool grouped;
+  decode_from_id(id, &dtype, &nt, &grouped, &geom);
+  snprintf(buf, sizeof(buf), "%s/nt%d/tn%dx64/kb%dx16/w%d/s%d/%s", dtype == 0 ? "__half" : "__nv_bfloat16", nt,
+           kGeom[geom].chunks, kGeom[geom].krows, kGeom[geom].warps, kGeom[geom].stages, grouped ? "true" : "false");
+  return buf;
+}
+
+constexpr int kPrefillBase = 1001;
 // tcgen05 ids: kPrefillBase + t (whole-K tiles, t < kPrefillWholeK), then
 // kPrefillBase + kPrefillWholeK + (t - kPrefillWholeK) * 4 + log2(cluster size) for the split-K tiles
 constexpr int kPrefillIds = kPrefillWholeK + (kPrefillTiles - kPrefillWholeK) * 4;
@@ -415,9 +310,6 @@ void prefill_from_id(int id, int* tile, int* S) {
   }
 }
 
-struct Geom { int chunks, krows; };
-const Geom kGeom[kGeoms] = {{2, 8}, {4, 8}, {4, 4}, {8, 4}, {4, 8}, {2, 8}, {2, 16}, {1, 16}, {3, 16}, {1, 32}};
-
 }  // namespace b200
 
 using namespace b200;
@@ -428,44 +320,37 @@ using namespace b200;
 extern "C" {
 
 const char* b200_w4a16_last_error(void) { return g_last_error.c_str(); }
-const char* b200_w4a16_version(void) { return "b200-w4a16 0.1 (sm_100a)"; }
+const char* b200_w4a16_version(void) { return "b200-w4a16 0.2 (sm_100a)"; }
 int64_t b200_w4a16_launch_count(void) { return g_launches.load(); }
-void b200_w4a16_debug_timeline(void* device_buf, int64_t launches) { stream_debug_timeline(device_buf, launches); }
-int b200_w4a16_set_pdl(int enable) { return g_default_pdl.exchange(enable ? 1 : 0); }
-
-int b200_w4a16_reduce_max_m(int64_t m) {
-  // mirror of marlin::determine_reduce_max_m(prob_m, max_par = 16), gptq_marlin_utils.cu:206-225
-  if (m <= 16) return 16;
-  if (m <= 32) return 32;
-  if (m <= 48) return 48;
-  if (m <= 64) return 64;
-  int64_t par = (m + 63) / 64;
-  if (par > 16) par = 16;
-  return static_cast<int>(64 * par);
+void b200_w4a16_debug_timeline(void* device_buf, int64_t launches) {
+  g_dbg_ts = static_cast<unsigned long long*>(device_buf);
+  g_dbg_ts_launches = device_buf ? launches : 0;
+  g_dbg_ts_next.store(0);
 }
+int b200_w4a16_set_pdl(int enable) { return g_default_pdl.exchange(enable ? 1 : 0); }
+int64_t b200_w4a16_set_scratch_capacity(int64_t bytes) { return g_scratch_capacity.exchange(bytes < 0 ? 0 : bytes); }
+
+int b200_w4a16_reduce_max_m(int64_t m) { return reduce_max_m(m); }
 
 int64_t b200_w4a16_workspace_ints(int64_t n) { return (n / 64) * 16; }
 
+// what the library touches when the caller guarantees only the reference contract
 int64_t b200_w4a16_reduce_bytes(int64_t m, int64_t n, int64_t k) {
   if (m <= 0 || n <= 0 || k <= 0 || n % 64 || k % 64) return -1;
   if (m > kStreamMaxM) return 0;  // the tcgen05 kernel accumulates in tensor memory: no scratch
-  const int rows = static_cast<int>(m < 32 ? m : 32);
-  // worst case over the geometries the heuristic (or force_config) may use
+  const long long contract = static_cast<long long>(reduce_max_m(m)) * n * 4;
+  return plan_decode(static_cast<int>(m), static_cast<int>(n), static_cast<int>(k), -1, contract, false).need_bytes;
+}
+
+// what full-width stream-K needs (worst case over the geometries force_config may select)
+int64_t b200_w4a16_reduce_bytes_fast(int64_t m, int64_t n, int64_t k) {
+  if (m <= 0 || n <= 0 || k <= 0 || n % 64 || k % 64) return -1;
+  const int mm = static_cast<int>(m < 32 ? m : 32);
   int64_t worst = 0;
   for (int geo = 0; geo < kGeoms; ++geo) {
-    const int tn = kGeom[geo].chunks * 64, kb = kGeom[geo].krows * 16;
-    if (k % kb) continue;
-    const long long ncols = (n + tn - 1) / tn, kblks = k / kb, units = ncols * kblks;
-    // worst case over the occupancies launch_decode may pick (1 .. g_v1_occ CTAs per SM)
-    for (int occ = 1; occ <= g_v1_occ; ++occ) {
-      const long long slots = static_cast<long long>(sm_count()) * occ;
-      const int grid = static_cast<int>(units < slots ? units : slots);
-      const int64_t b2 = ncols * decode_slot_max(static_cast<int>(kblks), units, grid) * rows * tn * 4ll;
-      if (b2 > worst) worst = b2;
-    }
-    const int grid = static_cast<int>(units < sm_count() ? units : sm_count());
-    const int64_t bytes = ncols * decode_slot_max(static_cast<int>(kblks), units, grid) * rows * tn * 4ll;
-    if (bytes > worst) worst = bytes;
+    if (!geom_fits(geo, static_cast<int>(n), static_cast<int>(k), false)) continue;
+    const DecodePlan pl = plan_decode(mm, static_cast<int>(n), static_cast<int>(k), geo, INT64_MAX / 4, false);
+    if (pl.need_bytes > worst) worst = pl.need_bytes;
   }
   return worst;
 }
@@ -484,20 +369,9 @@ int b200_w4a16_pick_config(int64_t m, int64_t n, int64_t k, int group_size, int 
     prefill_pick(g, &tile, &S);
     return prefill_id(tile, S);
   }
-  const int mm = static_cast<int>(m < 32 ? m : 32);
-  if (use_cluster_streamer(mm, n, k)) {
-    GemmCall g;
-    std::memset(&g, 0, sizeof(g));
-    g.m = mm;
-    g.n = static_cast<int>(n);
-    g.k = static_cast<int>(k);
-    g.group_size = group_size;
-    g.dtype = dtype;
-    int geom = 0, S = 1;
-    stream_pick(g, &geom, &S);
-    return kStreamBase + geom * 8 + (S - 1);
-  }
-  return 1 + decode_index(dtype, nt_for_m(mm), group_size != -1, pick_geometry(mm, (int)n, (int)k));
+  const int mm = static_cast<int>(m);
+  const DecodePlan pl = plan_decode(mm, static_cast<int>(n), static_cast<int>(k), -1, INT64_MAX / 4, false);
+  return decode_id(dtype, nt_for_m(mm), group_size != -1, pl.geom);
 }
 
 int b200_w4a16_max_clusters(int config, int64_t m, int group_size, int dtype) {
@@ -508,8 +382,6 @@ int b200_w4a16_max_clusters(int config, int64_t m, int group_size, int dtype) {
   g.k = 4096;
   g.group_size = group_size;
   g.dtype = dtype;
-  if (config >= kStreamBase && config < kStreamBase + kStreamGeoms * 8)
-    return stream_max_clusters(g, (config - kStreamBase) >> 3, 1 + ((config - kStreamBase) & 7));
   if (config >= kPrefillBase && config < kPrefillBase + kPrefillIds) {
     int tile, S;
     prefill_from_id(config, &tile, &S);
@@ -519,15 +391,13 @@ int b200_w4a16_max_clusters(int config, int64_t m, int group_size, int dtype) {
 }
 
 const char* b200_w4a16_config_name(int config) {
-  const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
   if (config >= kPrefillBase && config < kPrefillBase + kPrefillIds) {
     int tile, S;
     prefill_from_id(config, &tile, &S);
     return prefill_tile_name(tile);
   }
-  if (config >= kStreamBase && config < kStreamBase + kStreamGeoms * 8) return stream_geom_name((config - kStreamBase) >> 3);
-  if (config < 1 || config > count) return "";
-  return g_decode[config - 1].name;
+  if (config < 1 || config > kDecodeIds) return "";
+  return decode_name(config);
 }
 
 int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales, const int32_t* g_idx,
@@ -550,7 +420,7 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     return fail(B200_W4A16_EINVAL, "prob_k = %lld is not divisible by group_size = 128", (long long)k);
   if (m > INT32_MAX || n > INT32_MAX || k > INT32_MAX || m * n > (1ll << 40))
     return fail(B200_W4A16_EINVAL, "problem too large: MNK = [%lld, %lld, %lld]", (long long)m, (long long)n, (long long)k);
-  if (!a || !qweight || !c || !workspace || (group_size == 128 && !scales) || (group_size == -1 && !scales))
+  if (!a || !qweight || !c || !workspace || !scales)
     return fail(B200_W4A16_EINVAL, "null pointer argument (a/qweight/scales/workspace/c)");
   if (has_act_order) {
     if (!is_k_full)
@@ -576,107 +446,73 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
   }
 
   const bool grouped = group_size != -1;
-  const int count = static_cast<int>(sizeof(g_decode) / sizeof(g_decode[0]));
   const int forced = opts ? opts->force_config : 0;
   const bool gated = opts && opts->gated_silu != 0;
   if (gated) {
     // fused SiLU(gate) * up: served by the persistent streaming kernel (decode / tree-verify widths)
-    if (m > 32 || forced != 0)
-      return fail(B200_W4A16_EINVAL, "gated_silu is fused for M <= 32 with the default configuration (got M = %lld, force_config %d)", (long long)m, forced);
+    if (m > kStreamMaxM || forced >= kPrefillBase)
+      return fail(B200_W4A16_EINVAL, "gated_silu is fused for M <= %d (got M = %lld, force_config %d)", kStreamMaxM, (long long)m, forced);
     if (group_size != 128 || (n % 256) != 0)
       return fail(B200_W4A16_EINVAL, "gated_silu needs group_size 128 and N (= 2 x intermediate) a multiple of 256, got N = %lld", (long long)n);
     if (opts->bias || opts->residual || opts->out_scale != 0.0f)
       return fail(B200_W4A16_EINVAL, "gated_silu does not combine with bias / residual / out_scale");
     if (has_act_order) return fail(B200_W4A16_EINVAL, "gated_silu does not combine with act-order");
   }
+  GemmCall g;
+  g.a = a;
+  g.qweight = qweight;
+  g.scales = scales;
+  g.workspace = workspace;
+  g.c = c;
+  g.c_tmp = c_tmp;
+  g.bias = opts ? opts->bias : nullptr;
+  g.residual = opts ? opts->residual : nullptr;
+  g.out_scale = opts ? opts->out_scale : 0.0f;
+  g.gated = gated;
+  g.m = static_cast<int>(m);
+  g.n = static_cast<int>(n);
+  g.k = static_cast<int>(k);
+  g.group_size = group_size;
+  g.dtype = dtype;
+  g.pdl = opts ? (opts->pdl != 0) : (g_default_pdl.load(std::memory_order_relaxed) != 0);
+  g.stream = st;
   // ---- tensor-bound regime: one persistent tcgen05 launch for any M ----
-  if ((forced == 0 && m > kStreamMaxM) || (forced >= kPrefillBase && forced < kStreamBase)) {
+  if ((forced == 0 && m > kStreamMaxM) || forced >= kPrefillBase) {
     if (forced >= kPrefillBase + kPrefillIds)
       return fail(B200_W4A16_EINVAL, "force_config %d out of range", forced);
-    GemmCall g;
-    g.a = a;
-    g.qweight = qweight;
-    g.scales = scales;
-    g.workspace = workspace;
-    g.c = c;
-    g.c_tmp = c_tmp;
-    g.bias = opts ? opts->bias : nullptr;
-    g.residual = opts ? opts->residual : nullptr;
-    g.out_scale = opts ? opts->out_scale : 0.0f;
-    g.gated = false;
-    g.m = static_cast<int>(m);
-    g.n = static_cast<int>(n);
-    g.k = static_cast<int>(k);
-    g.group_size = group_size;
-    g.dtype = dtype;
-    g.pdl = opts ? (opts->pdl != 0) : (g_default_pdl.load(std::memory_order_relaxed) != 0);
-    g.stream = st;
     int tile, S;
     if (forced) prefill_from_id(forced, &tile, &S);
     else prefill_pick(g, &tile, &S);
     return launch_prefill(g, tile, S);
   }
-  // ---- streaming regime: needs the fp32 split-K scratch ----
-  {
-    const int64_t need = b200_w4a16_reduce_bytes(m < kStreamMaxM ? m : kStreamMaxM, n, k);
-    if (!c_tmp) return fail(B200_W4A16_EINVAL, "c_tmp (fp32 reduce scratch) is required");
-    if (opts && opts->c_tmp_bytes > 0 && opts->c_tmp_bytes < need)
-      return fail(B200_W4A16_EINVAL, "c_tmp too small: %lld bytes given, %lld needed for MNK = [%lld, %lld, %lld]",
-                  (long long)opts->c_tmp_bytes, (long long)need, (long long)m, (long long)n, (long long)k);
+  // ---- streaming regime ----
+  int geom = -1;
+  if (forced > 0) {
+    if (forced > kDecodeIds) return fail(B200_W4A16_EINVAL, "force_config %d out of range", forced);
+    int fdt, fnt;
+    bool fgr;
+    decode_from_id(forced, &fdt, &fnt, &fgr, &geom);
+    const int mm0 = static_cast<int>(m < 32 ? m : 32);
+    if (fdt != dtype || fgr != grouped || fnt * 8 < mm0 || !geom_fits(geom, g.n, g.k, gated))
+      return fail(B200_W4A16_EINVAL, "force_config %d (%s) does not fit m=%d k=%lld dtype=%d group=%d",
+                  forced, decode_name(forced), mm0, (long long)k, dtype, group_size);
   }
+  // scratch the caller guarantees: stated per call, or process-wide, or the reference's contract
+  // (determine_reduce_max_m(M, 16) x N floats; callers: w4a16_gptq_marlin_layer.cuh:34-37)
+  long long capacity = opts && opts->c_tmp_bytes > 0 ? opts->c_tmp_bytes : g_scratch_capacity.load(std::memory_order_relaxed);
+  if (capacity <= 0) capacity = static_cast<long long>(reduce_max_m(m)) * n * 4;
+  if (!c_tmp) capacity = 0;  // no scratch at all: whole-column launches only
   // ---- M loop: slabs of <= 32 tokens through the streaming kernel ----
   for (int64_t m0 = 0; m0 < m; m0 += 32) {
     const int mm = static_cast<int>(m - m0 < 32 ? m - m0 : 32);
-    int idx = -1;
-    if (forced >= kStreamBase || (forced == 0 && !gated && use_cluster_streamer(mm, n, k))) {
-      // cluster split-K streaming kernel
-    } else if (opts && opts->force_config > 0) {
-      idx = opts->force_config - 1;
-      if (idx >= count) return fail(B200_W4A16_EINVAL, "force_config %d out of range", opts->force_config);
-      const DecodeConfig& f = g_decode[idx];
-      if (f.dtype != dtype || f.grouped != grouped || f.nt * 8 < mm || k % (f.krows * 16) != 0)
-        return fail(B200_W4A16_EINVAL, "force_config %d (%s) does not fit m=%d k=%lld dtype=%d group=%d",
-                    opts->force_config, f.name, mm, (long long)k, dtype, group_size);
-    } else {
-      idx = decode_index(dtype, nt_for_m(mm), grouped, pick_geometry(mm, (int)n, (int)k));
-    }
-    GemmCall g;
-    g.a = static_cast<const char*>(a) + static_cast<size_t>(m0) * k * esz;
-    g.qweight = qweight;
-    g.scales = scales;
-    g.workspace = workspace;
-    g.c = static_cast<char*>(c) + static_cast<size_t>(m0) * n * esz;
-    g.c_tmp = c_tmp;
-    g.bias = opts ? opts->bias : nullptr;
-    g.residual = (opts && opts->residual)
-                     ? static_cast<const char*>(opts->residual) + static_cast<size_t>(m0) * n * esz
-                     : nullptr;
-    g.out_scale = opts ? opts->out_scale : 0.0f;
-    g.gated = gated;
-    g.m = mm;
-    g.n = static_cast<int>(n);
-    g.k = static_cast<int>(k);
-    g.group_size = group_size;
-    g.dtype = dtype;
-    g.pdl = opts ? (opts->pdl != 0) : (g_default_pdl.load(std::memory_order_relaxed) != 0);
-    g.stream = st;
-    if (idx < 0) {
-      int geom, S;
-      if (forced >= kStreamBase) {
-        geom = (forced - kStreamBase) >> 3;
-        S = 1 + ((forced - kStreamBase) & 7);
-        if (geom >= kStreamGeoms) return fail(B200_W4A16_EINVAL, "force_config %d out of range", forced);
-      } else {
-        stream_pick(g, &geom, &S);
-      }
-      if (int rc = launch_stream(g, geom, S)) return rc;
-      continue;
-    }
-    if (gated) {
-      if (int rc = launch_gated(g, nt_for_m(mm), pick_geometry(mm, (int)n, (int)k))) return rc;
-      continue;
-    }
-    if (int rc = g_decode[idx].launch(g)) return rc;
+    GemmCall s = g;
+    s.a = static_cast<const char*>(a) + static_cast<size_t>(m0) * k * esz;
+    s.c = static_cast<char*>(c) + static_cast<size_t>(m0) * (gated ? n / 2 : n) * esz;
+    s.residual = g.residual ? static_cast<const char*>(g.residual) + static_cast<size_t>(m0) * n * esz : nullptr;
+    s.m = mm;
+    const DecodePlan pl = plan_decode(mm, s.n, s.k, geom, capacity, gated);
+    const int nt = forced > 0 ? (1 << (((forced - 1) / kGeoms) % 3)) : nt_for_m(mm);
+    if (int rc = (dtype == 0 ? launch_decode_fp16(s, pl, nt) : launch_decode_bf16(s, pl, nt))) return rc;
   }
   return B200_W4A16_OK;
 }
@@ -689,15 +525,16 @@ int b200_w4a16_gemm(const void* a, const int32_t* qweight, const void* scales, c
                             is_k_full, has_act_order, a_tmp, c_tmp, stream, nullptr);
 }
 
-int b200_w4a16_linear_forward(const void* input, const int32_t* qweight, const void* scales, const void* bias,
-                              int32_t* workspace, void* output, void* tgt, int inplace, int64_t num_tokens,
-                              int64_t dim_out, int64_t dim_in, int group_size, int dtype, void* a_tmp,
-                              float* c_tmp, void* stream) {
+int b200_w4a16_linear_forward_ex(const void* input, const int32_t* qweight, const void* scales, const void* bias,
+                                 int32_t* workspace, void* output, void* tgt, int inplace, int64_t num_tokens,
+                                 int64_t dim_out, int64_t dim_in, int group_size, int dtype, void* a_tmp,
+                                 float* c_tmp, int64_t c_tmp_bytes, void* stream) {
   // W4A16GPTQMarlinLinear::prefill, w4a16_gptq_marlin_linear.cuh:104-146
   b200_w4a16_opts o;
   std::memset(&o, 0, sizeof(o));
   o.bias = bias;
   o.pdl = g_default_pdl.load(std::memory_order_relaxed);
+  o.c_tmp_bytes = c_tmp_bytes;
   void* dst = output;
   if (tgt && inplace) {
     o.residual = tgt;
@@ -709,6 +546,14 @@ int b200_w4a16_linear_forward(const void* input, const int32_t* qweight, const v
   return b200_w4a16_gemm_ex(input, qweight, scales, nullptr, nullptr, workspace, dst, num_tokens, dim_out,
                             dim_in, group_size, dtype, /*is_k_full=*/1, /*has_act_order=*/0, a_tmp, c_tmp,
                             stream, &o);
+}
+
+int b200_w4a16_linear_forward(const void* input, const int32_t* qweight, const void* scales, const void* bias,
+                              int32_t* workspace, void* output, void* tgt, int inplace, int64_t num_tokens,
+                              int64_t dim_out, int64_t dim_in, int group_size, int dtype, void* a_tmp,
+                              float* c_tmp, void* stream) {
+  return b200_w4a16_linear_forward_ex(input, qweight, scales, bias, workspace, output, tgt, inplace, num_tokens,
+                                      dim_out, dim_in, group_size, dtype, a_tmp, c_tmp, 0, stream);
 }
 
 int b200_w4a16_dequant(const int32_t* qweight, const void* scales, void* w_out, int64_t n, int64_t k,

@@ -33,17 +33,8 @@ int launch_one(const GemmCall& g, int S, int* query) {
   using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
   auto kern = w4a16_prefill_kernel<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
   static bool attr_set = false;  // benign race: idempotent
-  // Two split-K CTAs (87-110 KB each) share an SM.  Round 1 found 1-2 % wrong launches in exactly that situation:
-  // the dequantisers released a raw int4 slot right after ISSUING its shared-memory loads, and under the heavier
-  // load of two CTAs the TMA refill could land first (fixed in prefill_kernel.cuh: the slot is released after its
-  // words were used).  B200_W4A16_TC_CORESIDENT=0 keeps one CTA per SM (117 KB request) for debugging.
-  static const bool coresident = [] { const char* e = std::getenv("B200_W4A16_TC_CORESIDENT"); return !(e && e[0] == '0'); }();
-  // B200_W4A16_TC_PAD: 2 = every split-K launch is padded; 1 = only launches with more CTAs than SMs (CTAs of the
-  // SAME launch would share an SM; the next launch's CTAs may still co-reside under PDL); 0 = never
-  static const int pad_mode = [] { const char* e = std::getenv("B200_W4A16_TC_PAD"); return e ? std::atoi(e) : 2; }();
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         Cfg::SMEM_BYTES < 117 * 1024 ? 117 * 1024 : Cfg::SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess)
       return fail(B200_W4A16_ECUDA, "cudaFuncSetAttribute(smem=%d): %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
     attr_set = true;
@@ -115,8 +106,6 @@ int launch_one(const GemmCall& g, int S, int* query) {
   args.n_tiles = (g.n + Cfg::BN - 1) / Cfg::BN;
   args.m_tiles = (g.m + BM - 1) / BM;
   args.kblks = g.k / 64;
-  static const int dbg = [] { const char* e = std::getenv("B200_W4A16_DBG_TC"); return e ? std::atoi(e) : 0; }();
-  args.dbg = dbg;
   const long long tiles = static_cast<long long>(args.n_tiles) * args.m_tiles;
   int grid = static_cast<int>(tiles < sm_count() ? tiles : sm_count());
   if (SPLIT) {
@@ -129,9 +118,7 @@ int launch_one(const GemmCall& g, int S, int* query) {
   std::memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(Cfg::THREADS);
-  const bool pad = SPLIT && !coresident && Cfg::SMEM_BYTES < 117 * 1024 &&
-                   (pad_mode >= 2 || (pad_mode == 1 && grid > sm_count()));
-  cfg.dynamicSmemBytes = pad ? 117 * 1024 : Cfg::SMEM_BYTES;
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = g.stream;
   cudaLaunchAttribute attr[2];
   int na = 0;
@@ -200,9 +187,7 @@ void prefill_pick(const GemmCall& g, int* tile_out, int* S_out) {
     const int bm = kTiles[t].bm;
     const int tiles = ((n + 127) / 128) * ((m + bm - 1) / bm);
     const int kblks = g.k / 64;
-    // one CTA per SM (see launch_one: co-resident split-K CTAs are switched off), one wave when possible
-    static const bool coresident = [] { const char* e = std::getenv("B200_W4A16_TC_CORESIDENT"); return !(e && e[0] == '0'); }();
-    const int cap = coresident ? (2 * sms * 9) / 10 : sms;
+    const int cap = (2 * sms * 9) / 10;
     int s = 8;
     while (s > 1 && (kblks / s < 4 || tiles * s > cap)) s >>= 1;
     if (m <= 128 || tiles <= cap) {

@@ -71,11 +71,15 @@ class W4A16GPTQMarlinLinear:
         if tgt is None and self.output is None:
             self.init_output_ptr(None, num_tokens)
         out = self.output[:num_tokens] if self.output is not None else None
-        rc = _l.lib().b200_w4a16_linear_forward(
+        # the mirror is handed a tensor, so it can state the scratch size (a raw-pointer caller states it once
+        # with set_scratch_capacity, or gets the reference's contract)
+        c_tmp_bytes = 0 if c_tmp is None else c_tmp.numel() * c_tmp.element_size()
+        rc = _l.lib().b200_w4a16_linear_forward_ex(
             _l._ptr(input), _l._ptr(self.weight), _l._ptr(self.scales),
             _l._ptr(self.bias) if self.has_bias else None, _l._ptr(self.workspace),
             _l._ptr(out), _l._ptr(tgt), 1 if inplace else 0, num_tokens, self.dim_out, self.dim_in,
-            self.group_size, _l.dtype_code(self.dtype), _l._ptr(a_tmp), _l._ptr(c_tmp), _l._stream(stream))
+            self.group_size, _l.dtype_code(self.dtype), _l._ptr(a_tmp), _l._ptr(c_tmp), c_tmp_bytes,
+            _l._stream(stream))
         if rc:
             _l._raise(rc)
         return tgt if tgt is not None else out

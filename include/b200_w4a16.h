@@ -49,7 +49,9 @@ typedef struct b200_w4a16_opts {
    *   if (out_scale) out = RN_T(out * T(out_scale))   */
   const void* bias;      /* T[N] or NULL                        (batched_add, src/model/elementwise.cuh:8-14)  */
   const void* residual;  /* T[M][N] or NULL; may alias `c`      (elementwise_add, src/model/elementwise.cuh:17-23) */
-  int64_t c_tmp_bytes;   /* size of c_tmp if known (validated), or 0 = caller guarantees b200_w4a16_reduce_bytes() */
+  int64_t c_tmp_bytes;   /* bytes of c_tmp the caller guarantees for THIS call; 0 = the process-wide capacity
+                          * (b200_w4a16_set_scratch_capacity) or, if none was set, the reference contract
+                          * determine_reduce_max_m(M, 16) x N floats.  The library never touches more. */
   int force_config;      /* 0 = heuristic; >0 = kernel configuration id (tuning / tests only)        */
   int pdl;               /* 1 = launch with programmatic dependent launch (prologue overlaps the previous kernel) */
   /* residual scaling of the layer (elementwise_scale(output, residual_scale) right after o_proj / before the
@@ -77,7 +79,12 @@ typedef struct b200_w4a16_opts {
  *   workspace     int32[(N/64)*16], zero on entry, zero again when the call completes
  *                 (reference lock contract: marlin_device_ops.cuh:347-377; w4a16_gptq_marlin_linear.cuh:76)
  *   a_tmp         T[M][K] scratch, touched only when has_act_order
- *   c_tmp         fp32 split-K scratch of at least b200_w4a16_reduce_bytes(m, n, k) bytes
+ *   c_tmp         fp32 split-K scratch, sized by the reference's rule: determine_reduce_max_m(M, 16) x N floats
+ *                 (gptq_marlin_utils.cu:206-225; callers w4a16_gptq_marlin_layer.cuh:34-37).  The library stays
+ *                 inside that bound; it only uses more (full-width stream-K, see b200_w4a16_reduce_bytes_fast)
+ *                 when the caller has declared a larger buffer with b200_w4a16_set_scratch_capacity() or
+ *                 opts->c_tmp_bytes.  `workspace` and `c_tmp` belong to ONE call at a time: two calls in flight on
+ *                 different streams need their own (the reference has a single stream, src/utils.cu:7).
  * Constraints (as the reference, gptq_marlin.cu:71-72, gptq_marlin_mm.cu:53-54,103-131):
  *   M,N,K > 0;  N % 64 == 0;  K % 64 == 0;  group_size in {128, -1};  K % 128 == 0 when group_size == 128. */
 int b200_w4a16_gemm(const void* a, const int32_t* qweight, const void* scales,
@@ -101,6 +108,14 @@ int b200_w4a16_linear_forward(const void* input, const int32_t* qweight, const v
                               const void* bias, int32_t* workspace, void* output, void* tgt,
                               int inplace, int64_t num_tokens, int64_t dim_out, int64_t dim_in,
                               int group_size, int dtype, void* a_tmp, float* c_tmp, void* stream);
+
+/* Same with the size of c_tmp stated (0 = as b200_w4a16_linear_forward); used by the Python operator mirror,
+ * which knows the size of the tensor it is handed. */
+int b200_w4a16_linear_forward_ex(const void* input, const int32_t* qweight, const void* scales,
+                                 const void* bias, int32_t* workspace, void* output, void* tgt,
+                                 int inplace, int64_t num_tokens, int64_t dim_out, int64_t dim_in,
+                                 int group_size, int dtype, void* a_tmp, float* c_tmp, int64_t c_tmp_bytes,
+                                 void* stream);
 
 /* W[K][N] = RN_T(T(q - 8) * T(scale)) written out in T: the bit-exact dequantisation the GEMM
  * kernels apply in registers (reference device code: marlin_device_ops.cuh:91-137, 294-303).
@@ -158,19 +173,25 @@ int b200_w4a16_allreduce(const void* const* peer_in, void* const* peer_res, int3
  * Returns the previous setting.  Initial value: environment variable B200_W4A16_PDL (default 0). */
 int b200_w4a16_set_pdl(int enable);
 
-/* Sizing helpers.
+/* Sizing helpers and the scratch contract.
  * b200_w4a16_reduce_max_m  == marlin::determine_reduce_max_m(prob_m, 16) (gptq_marlin_utils.cu:206-225).
- * b200_w4a16_reduce_bytes  bytes of c_tmp this library needs for (m, n, k) on the current device.  The
- *                          reference's callers size c_tmp ONCE for their maximum token count
- *                          (chunk_length, >= 1024 by default): reduce_max_m(chunk) * 2*intermediate floats
- *                          per layer (w4a16_gptq_marlin_layer.cuh:34-37; 128 MiB for MiniCPM4-8B) and
- *                          reduce_max_m(chunk) * 2*hidden floats for EAGLE (minicpm4_eagle.cuh:134-137;
- *                          32 MiB).  This library needs at most 16 MiB for any m <= 64 on those shapes,
- *                          so those buffers are always large enough; a caller that sizes c_tmp per call
- *                          must use this function instead of reduce_max_m(m) * n.
+ * b200_w4a16_reduce_bytes  bytes of c_tmp the library touches for (m, n, k) when the caller guarantees only the
+ *                          reference contract; always <= reduce_max_m(m) * n * 4.  Inside that bound the split
+ *                          columns of the stream-K kernel get at most reduce_max_m(m) / m fp32 slots; where that
+ *                          is not enough the launch uses fewer CTAs or whole columns per CTA (slower, no scratch).
+ * b200_w4a16_reduce_bytes_fast  bytes full-width stream-K needs (<= 16 MiB for m <= 32 on the MiniCPM4-8B shapes).
+ * b200_w4a16_set_scratch_capacity(bytes)  process-wide promise: every c_tmp passed to an entry point without a size
+ *                          (b200_w4a16_gemm, b200_w4a16_linear_forward, the gptq_marlin_gemm shim) has at least
+ *                          `bytes` bytes.  CPM.cu allocates reduce_max_m(chunk_length) * 2*intermediate floats per
+ *                          model (w4a16_gptq_marlin_layer.cuh:34-37: 128 MiB for MiniCPM4-8B at chunk 1024) and
+ *                          reduce_max_m(chunk) * 2*hidden floats for EAGLE (minicpm4_eagle.cuh:134-137): an
+ *                          integration calls this once after init_storage with the smaller of the two.  0 (default)
+ *                          = the reference contract only.  Returns the previous value.
  * b200_w4a16_workspace_ints == (n / 64) * 16 (w4a16_gptq_marlin_linear.cuh:76). */
 int b200_w4a16_reduce_max_m(int64_t m);
 int64_t b200_w4a16_reduce_bytes(int64_t m, int64_t n, int64_t k);
+int64_t b200_w4a16_reduce_bytes_fast(int64_t m, int64_t n, int64_t k);
+int64_t b200_w4a16_set_scratch_capacity(int64_t bytes);
 int64_t b200_w4a16_workspace_ints(int64_t n);
 
 /* Introspection: kernels launched by this library since load (for bench.py's gpu_launches),

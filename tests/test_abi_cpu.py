@@ -42,13 +42,29 @@ def test_host_helpers_match_reference_sizing(lib):
         assert lib.b200_w4a16_reduce_max_m(m) == mo.determine_reduce_max_m(m)
     assert lib.b200_w4a16_workspace_ints(4096) == 64 * 16
     assert lib.b200_w4a16_version().decode().startswith("b200-w4a16")
-    # c_tmp: the reference's callers allocate it once for chunk_length tokens (>= 1024): at least
-    # reduce_max_m(1024) * 2*hidden floats = 32 MiB (minicpm4_eagle.cuh:134-137); we must fit in that
-    for m in (1, 4, 16, 64, 354, 1024):
-        for k, n in ((4096, 4608), (4096, 4096), (4096, 32768), (16384, 4096)):
-            need = lib.b200_w4a16_reduce_bytes(m, n, k)
-            assert 0 <= need <= 16 << 20, (m, k, n, need)
     assert lib.b200_w4a16_reduce_bytes(1, 100, 128) == -1
+
+
+SHAPES_8B = ((4096, 4608), (4096, 4096), (4096, 32768), (16384, 4096))
+SHAPES_70B = ((8192, 10240), (8192, 8192), (8192, 57344), (28672, 8192))
+# tensor-parallel shards of the 70B shapes (column-parallel N/tp, row-parallel K/tp) at tp = 2, 4, 8
+SHARDS_70B = tuple((k, n // tp) for tp in (2, 4, 8) for k, n in (SHAPES_70B[0], SHAPES_70B[2])) + \
+    tuple((k // tp, n) for tp in (2, 4, 8) for k, n in (SHAPES_70B[1], SHAPES_70B[3]))
+
+
+def test_scratch_stays_inside_the_reference_contract(lib):
+    """c_tmp: the reference's rule is determine_reduce_max_m(M, 16) x N floats (gptq_marlin_utils.cu:206-225;
+    callers: w4a16_gptq_marlin_layer.cuh:34-37).  What the library touches without a declared capacity must fit in
+    it for EVERY M; the fast path's need is reported separately and fits CPM.cu's real allocations
+    (>= reduce_max_m(1024) * 2*hidden floats = 32 MiB, minicpm4_eagle.cuh:134-137)."""
+    for k, n in SHAPES_8B + SHAPES_70B + SHARDS_70B + ((128, 64), (640, 448), (1152, 1024)):
+        for m in list(range(1, 34)) + [48, 64, 65, 354, 1024, 4096]:
+            need = lib.b200_w4a16_reduce_bytes(m, n, k)
+            assert 0 <= need <= lib.b200_w4a16_reduce_max_m(m) * n * 4, (m, k, n, need)
+            fast = lib.b200_w4a16_reduce_bytes_fast(m, n, k)
+            assert 0 <= fast <= 32 << 20, (m, k, n, fast)
+    prev = lib.b200_w4a16_set_scratch_capacity(1 << 27)
+    assert prev == 0 and lib.b200_w4a16_set_scratch_capacity(0) == 1 << 27
 
 
 def test_missing_library_fails_loudly(monkeypatch):
