@@ -125,7 +125,7 @@ class OursArm:
         return lin
 
     def scratch_floats(self, m, n, k):
-        return self.B.reduce_bytes(m, n, k) // 4
+        return self.B.reduce_bytes_fast(m, n, k) // 4
 
     def run(self, lin, m, a, out, c_tmp, stream):
         lin.prefill(stream, m, a, None, c_tmp, tgt=out)
@@ -210,6 +210,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-detail", action="store_true")
     ap.add_argument("--no-lm-head", action="store_true", help="skip the un-quantised lm_head leg (SURVEY 8f-2)")
+    ap.add_argument("--no-prefill", action="store_true", help="skip the chunked-prefill leg (BASELINE.json configs[2])")
+    ap.add_argument("--prefill-m", default="1024,4096,354", help="chunk sizes of the prefill leg (354 = 106850 %% 2048, the ragged last chunk)")
+    ap.add_argument("--prefill-layers", type=int, default=4)
+    ap.add_argument("--no-tp1", action="store_true", help="skip the unsharded Llama-3-70B record (the tp = 1 base of the scaling curve)")
     ap.add_argument("--workload", default="auto", choices=["auto", "minicpm4", "llama70b"],
                     help="auto: MiniCPM4-8B linears at N=1, tensor-parallel Llama-3-70B linears at N>1")
     ap.add_argument("--collective", default="oneshot", choices=["oneshot", "nccl"],
@@ -373,13 +377,9 @@ def main():
     low = [m for m in widths if m <= 32] or widths
     low_ms = sum(per_width_ms[m] for m in low)
     achieved = pass_bytes * len(low) / (low_ms * 1e-3) / 1e9
-    traffic, traffic_note = None, ""
-    tpath = os.path.join(ROOT, "profiles", "r01", "d_traffic.json")
-    if not use_ref_kernel and os.path.exists(tpath):  # DRAM bytes of the dominant launch from the committed ncu capture
-        tj = json.load(open(tpath))
-        traffic = tj["traffic"]
-        traffic_note = (f"; traffic = ncu dram read+write bytes of one {tj['launch']} launch "
-                        f"(algorithmic {tj['algorithmic_bytes']} B)")
+    # traffic: DRAM bytes need ncu counters, which bench.py does not collect (a number taken under a profiler is not
+    # a bench value); the per-round capture is committed under profiles/ and quoted in DESIGN.md
+    traffic, traffic_note = None, "; traffic: null here (ncu capture of the current kernel: see profiles/r02)"
     roofline = dict(bound="hbm", achieved=round(achieved, 1), peak=pk["hbm"], unit="GB/s",
                     frac=round(achieved / pk["hbm"], 4), traffic=traffic,
                     kernel="w4a16_decode_kernel" if not use_ref_kernel else "marlin::Marlin",
@@ -415,11 +415,86 @@ def main():
     if use_ref_kernel:
         line["impl"] = "reference"
         line["roofline"]["note"] += "; this is the reference's kernel, reported for comparison"
+    if not args.no_prefill:
+        line["prefill"] = prefill_leg(torch, dev, arm, stream, pk, local_rank,
+                                      [int(x) for x in args.prefill_m.split(",")], args.prefill_layers)
     if not args.no_lm_head:
         line["lm_head"] = lm_head_leg(torch, dev, stream, widths, pk, ours=not use_ref_kernel)
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(torch, [q[0] for q in qw], [s[0] for s in sc], SHAPES_8B, 16)
+    if not args.no_tp1:
+        # the unsharded Llama-3-70B linears (configs[4]) on ONE GPU: the tp = 1 base of the 1 -> 8 scaling curve
+        del qw, sc, lins, graphs, acts, outs
+        torch.cuda.empty_cache()
+        from bench_tp import measure_tp
+        t1 = measure_tp(args, torch, dev, None, 0, 1, local_rank, use_reference=use_ref_kernel, steps=max(3, K // 4))
+        line["llama70b_tp1"] = {"value": t1["value"], "unit": "GB/s", "ms_per_step": t1["ms_per_step"],
+                                "per_width": t1["per_width"], "workload": t1["config"]["workload"]}
     print(json.dumps(line), flush=True)
+
+
+def prefill_leg(torch, dev, arm, stream, pk, gpu_index, ms, layers, seconds=1.5):
+    """BASELINE.json configs[2]: chunked prefill.  The four MiniCPM4-8B linears x `layers` layers (distinct weights:
+    4 layers = 489 MB > L2) at chunk sizes M, one CUDA graph per M, replayed back to back for >= `seconds` seconds so
+    that the number is a SUSTAINED one under the power cap and the clock sampler sees the region.  Same harness for
+    both arms: ours = one persistent tcgen05 launch per linear; reference = marlin_mm's `par` M loop
+    (gptq_marlin_mm.cu:161-206).  TFLOP/s = 2*M*N*K / device time, against the measured dense bf16 peaks of
+    MEASURED_PEAKS.json (burst: a kernel timed alone; sustained: inside a long loop) and the nominal 2250."""
+    g = torch.Generator(device=dev).manual_seed(4321)
+    qw, sc, lins = [], [], []
+    for name, k, n in SHAPES_8B:
+        q = torch.randint(-2**31, 2**31 - 1, (layers, k // 16, 2 * n), dtype=torch.int32, device=dev, generator=g)
+        s = (torch.rand((layers, k // GROUP, n), device=dev, generator=g) * 0.018 + 0.002).half()
+        qw.append(q)
+        sc.append(s)
+        lins.append([arm.make_linear(k, n, q[l], s[l]) for l in range(layers)])
+    out = {}
+    for m in ms:
+        acts = [torch.randn((m, k), device=dev, generator=g).half() for _, k, n in SHAPES_8B]
+        outs = [torch.empty((m, n), dtype=torch.float16, device=dev) for _, k, n in SHAPES_8B]
+        c_tmp = torch.empty(max(arm.scratch_floats(m, n, k) for _, k, n in SHAPES_8B) + 64, dtype=torch.float32, device=dev)
+
+        def chain():
+            for l in range(layers):
+                for i in range(4):
+                    arm.run(lins[i][l], m, acts[i], outs[i], c_tmp, stream)
+        chain()
+        stream.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=stream):
+            chain()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        best = 1e30
+        for _ in range(3):   # warm-up, also the burst figure (a replay timed alone)
+            e0.record(stream)
+            gr.replay()
+            e1.record(stream)
+            stream.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        reps = max(5, int(seconds * 1e3 / best))
+        sampler = ClockSampler(gpu_index)
+        sampler.start()
+        torch.cuda.synchronize()
+        e0.record(stream)
+        for _ in range(reps):
+            gr.replay()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        clocks = sampler.stop()
+        ms_layer = e0.elapsed_time(e1) / reps / layers
+        flops = sum(2.0 * m * k * n for _, k, n in SHAPES_8B)
+        tf = flops / (ms_layer * 1e-3) / 1e12
+        tf_burst = flops / (best / layers * 1e-3) / 1e12
+        out[str(m)] = dict(us_per_layer=round(ms_layer * 1e3, 2), tflops=round(tf, 1),
+                           frac_burst=round(tf / pk["tf_burst"], 4), frac_sustained=round(tf / pk["tf_sustained"], 4),
+                           frac_nominal_2250=round(tf / 2250.0, 4), replays=reps,
+                           tflops_first_replays=round(tf_burst, 1), clocks=clocks)
+        del gr, acts, outs, c_tmp
+    return {"workload": f"chunked prefill: MiniCPM4-8B W4A16 linears (qkv, o, gate_up, down) x {layers} layers at chunk sizes "
+                        f"M={ms}; one CUDA graph per M replayed back to back for >= {seconds} s (sustained, power cap included)",
+            "kernel": arm.name, "peaks": {"burst": pk["tf_burst"], "sustained": pk["tf_sustained"], "nominal": 2250.0,
+                                          "source": pk["source"]},
+            "per_m": out}
 
 
 def lm_head_leg(torch, dev, stream, widths, pk, ours, reps=16, iters=5):

@@ -36,29 +36,73 @@ def local_dims(k, n, style, parts, rank, world):
     return k1 - k0, n
 
 
-def main_tp(args, rank, world, local_rank, use_reference=False):
-    import torch
-    import torch.distributed as dist
-    from bench import ClockSampler, peaks
+def check_tp_result(torch, dist, dev, world, rank, widths, ar, stream):
+    """Outside the timed region, once per width: a tensor-parallel layer computed from REAL shards of one full
+    weight (cpmcu_b200/sharding.py) must equal the unsharded GEMM of this library — column-parallel: the rank's
+    column slices; row-parallel + all-reduce: the full output, identical on every rank."""
+    import cpmcu_b200 as B
+    from cpmcu_b200 import sharding as sh
+    report = {}
+    for name, k, n, style, parts in (("qkv", 8192, 10240, "col", [8192, 1024, 1024]), ("o", 8192, 8192, "row", None)):
+        g = torch.Generator(device=dev).manual_seed(99)           # same seed on every rank: identical full tensors
+        q = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=dev, generator=g)
+        s = (torch.rand((k // GROUP, n), device=dev, generator=g) * 0.018 + 0.002).half()
+        ws = torch.zeros((n // 64) * 16, dtype=torch.int32, device=dev)
+        for m in widths:
+            a = torch.randn((m, k), device=dev, generator=g).half()
+            ct = torch.empty(B.reduce_bytes_fast(m, n, k) // 4 + 64, dtype=torch.float32, device=dev)
+            full = B.gemm(a, q, s, ws, ct, stream=stream)
+            if style == "col":
+                ql, sl = sh.shard_fused_columns(q, s, parts, rank, world)
+                loc = B.gemm(a, ql, sl, ws, ct, stream=stream)
+                cols, off = [], 0
+                for p in parts:
+                    b, e = sh.even_split(p, world, rank, 64)
+                    cols.append(full[:, off + b:off + e])
+                    off += p
+                want = torch.cat(cols, dim=1)
+                stream.synchronize()
+                err = float((loc.float() - want.float()).abs().max())
+                ok = err <= 1e-2 * float(want.float().abs().mean()) + 1e-3   # split-K order differs between the two launches
+            else:
+                k0, k1 = sh.even_split(k, world, rank, 128)
+                ql, sl = sh.shard_rows(q, s, k0, k1)
+                al = a[:, k0:k1].contiguous()
+                out = torch.empty((m, n), dtype=torch.float16, device=dev)
+                if ar is not None:
+                    buf = ar.next_input(m, n)
+                    B.gemm(al, ql, sl, ws, ct, out=buf, stream=stream)
+                    ar.reduce(buf, out, stream=stream)
+                else:
+                    B.gemm(al, ql, sl, ws, ct, out=out, stream=stream)
+                    stream.synchronize()
+                    dist.all_reduce(out)
+                stream.synchronize()
+                torch.cuda.synchronize()
+                err = float((out.float() - full.float()).abs().max())
+                # partials are rounded to fp16 before the fp32 sum: W roundings instead of one
+                ok = err <= 1e-2 * float(full.float().abs().mean()) * max(1, world) ** 0.5 + 1e-3
+                gathered = [torch.empty_like(out) for _ in range(world)]
+                dist.all_gather(gathered, out)
+                ok = ok and all(torch.equal(gathered[0], t) for t in gathered)   # bit-identical on every rank
+            report[f"{name}/m{m}"] = round(err, 5)
+            if not ok:
+                raise RuntimeError(f"[rank {rank}] tensor-parallel {name} at M={m} differs from the unsharded GEMM: max abs err {err}")
+    return report
 
-    if use_reference and rank != 0:
-        return  # the reference arm is one process on one GPU; the other ranks exit without work
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1 and not use_reference:
-        dist.init_process_group("nccl", device_id=dev)
+
+def measure_tp(args, torch, dev, dist, rank, world, local_rank, use_reference=False, steps=None):
+    """one measurement of the Llama-3-70B linears over `world` ranks (world = 1: unsharded on this GPU); returns the
+    JSON line as a dict on every rank (values are max-over-ranks)."""
+    from bench import ClockSampler, peaks
     pk = peaks()
     widths = [int(x) for x in args.tp_widths.split(",")]
     L = args.tp_layers
-
+    eff_world, eff_rank = world, rank
     if use_reference:
-        # the reference has no multi-GPU path: rank 0 runs the UNSHARDED model on one GPU through the
-        # unmodified reference Marlin kernel; the other ranks exit without work
-        eff_world, eff_rank = 1, 0
         from oracle import ref_marlin
         ref_marlin.lib()
     else:
-        eff_world, eff_rank = world, rank
         import cpmcu_b200 as B
         B.lib()
         B.set_pdl(not args.no_pdl)
@@ -84,7 +128,7 @@ def main_tp(args, rank, world, local_rank, use_reference=False):
     if use_reference:
         scratch = max(ref_marlin.reduce_max_m(m) * d["n"] for m in widths for d in lins)
     else:
-        scratch = max(B.reduce_bytes(m, d["n"], d["k"]) // 4 for m in widths for d in lins)
+        scratch = max(B.reduce_bytes_fast(m, d["n"], d["k"]) // 4 for m in widths for d in lins)
     c_tmp = torch.empty(scratch + 64, dtype=torch.float32, device=dev)
     n_launch = [0]
 
@@ -108,6 +152,9 @@ def main_tp(args, rank, world, local_rank, use_reference=False):
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)   # every rank must take the same path
         if int(flag.item()) == 0:
             ar, collective = None, "NCCL all-reduce (fp16, sum) inside the CUDA graph"
+    tp_check = None
+    if eff_world > 1 and not use_reference:
+        tp_check = check_tp_result(torch, dist, dev, eff_world, eff_rank, widths, ar, stream)
 
     def gemm(i, l, m, out):
         d = lins[i]
@@ -158,15 +205,15 @@ def main_tp(args, rank, world, local_rank, use_reference=False):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
+    def timed(fn, nsteps):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        for _ in range(steps):
+        for _ in range(nsteps):
             fn()
         e1.record(stream)
         barrier()
-        ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+        ms = torch.tensor([e0.elapsed_time(e1) / nsteps], device=dev)
         if eff_world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
@@ -184,7 +231,7 @@ def main_tp(args, rank, world, local_rank, use_reference=False):
 
     for _ in range(max(args.warmup, 3)):
         kernel_step()
-    K = args.steps
+    K = steps if steps else args.steps
     sampler = ClockSampler(local_rank)
     sampler.start()
     ms_per_step = timed(kernel_step, K)
@@ -202,13 +249,10 @@ def main_tp(args, rank, world, local_rank, use_reference=False):
         e2e_step()
     e2e_ms = timed(e2e_step, K)
     clocks = sampler.stop()
+    if ar is not None:
+        ar.check()   # a peer that never arrived is an error (NaN output + error word), never a silently wrong sum
     if eff_world > 1:
         dist.barrier()
-    if rank != 0:
-        # leave without tearing NCCL down: destroying a communicator whose collectives were captured in
-        # live CUDA graphs can hang (seen on the first 2-GPU run); the process is done anyway
-        sys.stdout.flush()
-        os._exit(0)
 
     step_bytes = model_bytes * len(widths)
     value = step_bytes / (ms_per_step * 1e-3) / 1e9
@@ -240,13 +284,54 @@ def main_tp(args, rank, world, local_rank, use_reference=False):
                              f"{eff_world} x {pk['hbm']} GB/s ({pk['source']})"},
         "clocks": clocks,
     }
+    if tp_check is not None:
+        line["tp_result_check"] = {"max_abs_err_vs_unsharded": tp_check,
+                                   "note": "sharded (sharding.py) vs unsharded GEMM of one full 70B qkv / o weight per width, "
+                                           "outside the timed region; row-parallel result bit-identical on every rank"}
+    del graphs, graphs_nocomm, graphs_comm, lins, acts, outs, c_tmp
+    torch.cuda.empty_cache()
+    return line
+
+
+def main_tp(args, rank, world, local_rank, use_reference=False):
+    import torch
+    import torch.distributed as dist
+
+    if use_reference and rank != 0:
+        return  # the reference arm is one process on one GPU; the other ranks exit without work
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1 and not use_reference:
+        dist.init_process_group("nccl", device_id=dev)
     if use_reference:
+        # the reference has no multi-GPU path: rank 0 runs the UNSHARDED model on one GPU through the
+        # unmodified reference Marlin kernel; the other ranks exit without work
+        line = measure_tp(args, torch, dev, None, 0, 1, local_rank, use_reference=True)
+        line["n_gpus"] = world
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": line["value"], "unit": "GB/s", "cores": 0, "kind": "reference",
                                 "sample": "GPU kernel of the reference (it has no CPU implementation of this path): "
                                           "oracle/_ref/libmarlin_ref.so, unsharded model on rank 0"}
+        print(json.dumps(line), flush=True)
+        return
+    # the tp = 1 base of the scaling curve: THIS library, unsharded, same layers and widths, on rank 0's GPU
+    tp1 = None
+    if rank == 0 and world > 1:
+        tp1 = measure_tp(args, torch, dev, None, 0, 1, local_rank, steps=max(3, args.steps // 4))
+    if world > 1:
+        dist.barrier()
+    line = measure_tp(args, torch, dev, dist if world > 1 else None, rank, world, local_rank)
+    if rank != 0:
+        # leave without tearing NCCL down: destroying a communicator whose collectives were captured in
+        # live CUDA graphs can hang (seen on the first 2-GPU run); the process is done anyway
+        sys.stdout.flush()
+        os._exit(0)
+    if tp1 is not None:
+        line["llama70b_tp1"] = {"value": tp1["value"], "unit": "GB/s", "ms_per_step": tp1["ms_per_step"],
+                                "per_width": tp1["per_width"]}
+        line["efficiency_vs_own_tp1"] = round(line["value"] / (world * tp1["value"]), 4)
     print(json.dumps(line), flush=True)
-    if eff_world > 1:
+    if world > 1:
         sys.stdout.flush()
         time.sleep(0.2)
         os._exit(0)

@@ -57,9 +57,19 @@ class OneShotAllReduce:
         self._in = [PtrArr(*[int(p) + i * max_elems * esz for p in hd.buffer_ptrs]) for i in range(2)]
         self._res = [PtrArr(*[int(p) + i * max_elems * esz for p in hr.buffer_ptrs]) for i in range(2)]
         self._sig = [PtrArr(*[int(p) + i * 2 * MAX_BLOCKS * MAX_WORLD * 4 for p in hs.buffer_ptrs]) for i in range(2)]
-        self.epoch = torch.zeros((2, 2 * MAX_BLOCKS), dtype=torch.int32, device=device)
+        # per buffer set: int32[2 * MAX_BLOCKS] barrier epochs + the sticky error word (+ padding)
+        self.epoch = torch.zeros((2, 2 * MAX_BLOCKS + 8), dtype=torch.int32, device=device)
         self._handles = (hd, hr, hs)
         self._turn = 0
+
+    def check(self):
+        """raises if any reduce() so far saw a peer that never arrived (its output was filled with NaN);
+        synchronises the device — call it outside timed / captured regions"""
+        import torch
+        torch.cuda.synchronize(self.device)
+        if int(self.epoch[:, 2 * MAX_BLOCKS].max().item()) != 0:
+            raise RuntimeError(f"one-shot all-reduce: a peer of rank {self.rank} did not arrive within 2 s "
+                               "(dead or desynchronised rank); the affected outputs are NaN")
 
     def next_input(self, m: int, n: int):
         """the symmetric buffer the NEXT reduce() will read, viewed as [m, n]"""

@@ -112,31 +112,48 @@ __device__ __forceinline__ uint4 ld_relaxed_sys_v4(const void* p) {
 
 constexpr int kArMaxWorld = 8;
 constexpr int kArMaxBlocks = 128;
+constexpr int kArErrIndex = 2 * kArMaxBlocks;        // epoch[kArErrIndex]: sticky error word of this rank
+constexpr unsigned long long kArTimeoutNs = 2000000000ull;  // a peer that is 2 s late is treated as dead
 
 struct AllReduceArgs {
   const void* in[kArMaxWorld];  // every rank's symmetric input buffer (peer-mapped addresses)
   void* res[kArMaxWorld];       // two-shot only: every rank's symmetric result buffer
   int* sig[kArMaxWorld];        // every rank's signal pad: int[2][kArMaxBlocks][kArMaxWorld]
-  int* epoch;                   // local: int[2][kArMaxBlocks], barriers completed per phase bank and block
+  int* epoch;                   // local: int[2][kArMaxBlocks] barriers completed per phase bank and block, then
+                                // int[1] error word (kArErrIndex): set when a peer never arrived
   void* out;                    // local T[elems]
   long long elems;
   int rank, world;
 };
 
 // all peers' block b tell each other "phase reached" (fire-and-forget red.release.sys on the peer's
-// counter) and wait until every peer has said so; `phase` selects the counter bank
-__device__ __forceinline__ void ar_block_barrier(const AllReduceArgs& a, int b, int phase, int target) {
+// counter) and wait until every peer has said so; `phase` selects the counter bank.  Returns false when a
+// peer did not arrive within kArTimeoutNs (a rank died or never launched): the caller then raises the error
+// word, poisons its output and leaves the epoch alone — a late or dead peer is an ERROR, never a wrong sum.
+__device__ __forceinline__ bool ar_block_barrier(const AllReduceArgs& a, int b, int phase, int target) {
+  __shared__ int s_ok;
+  if (threadIdx.x == 0) s_ok = 1;
+  __syncthreads();
   if (threadIdx.x < a.world) {
     const int w = threadIdx.x;
     const int slot = (phase * kArMaxBlocks + b) * kArMaxWorld;
     asm volatile("red.release.sys.global.add.s32 [%0], 1;" ::"l"(a.sig[w] + slot + a.rank) : "memory");
     const int* mine = a.sig[a.rank] + slot + w;
-    // bounded: a peer that never arrives (a rank died) must not hang this GPU — give up after ~1 s;
-    // the sums are then wrong and the caller's collective error handling takes over
-    for (long long spin = 0; ld_acquire_sys(mine) - target < 0 && spin < (1ll << 24); ++spin) {
+    unsigned long long t0 = 0;
+    for (unsigned spin = 0; ld_acquire_sys(mine) - target < 0; ++spin) {
+      if ((spin & 1023u) == 1023u) {   // look at the clock once in a while
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t0 == 0) t0 = t;
+        if (t - t0 > kArTimeoutNs) {
+          s_ok = 0;
+          break;
+        }
+      }
     }
   }
   __syncthreads();
+  return s_ok != 0;
 }
 
 // fp32 sum, in rank order, of the 8 elements at offset i of every rank's input
@@ -183,9 +200,17 @@ allreduce_kernel(const AllReduceArgs a) {
   pdl_launch_dependents();
   pdl_wait_prior_grids();
   const int target = a.epoch[b] + 1;
-  ar_block_barrier(a, b, 0, target);
   const long long tid8 = (static_cast<long long>(b) * blockDim.x + threadIdx.x) * 8;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * 8;
+  auto fail_out = [&]() {   // error word + NaN output for this block's share; the epoch is NOT advanced
+    if (threadIdx.x == 0) atomicExch(a.epoch + kArErrIndex, 1);
+    const uint4 nan4 = make_uint4(0x7fff7fffu, 0x7fff7fffu, 0x7fff7fffu, 0x7fff7fffu);  // NaN in fp16 and bf16
+    for (long long i = tid8; i < a.elems; i += stride) *reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.out) + i) = nan4;
+  };
+  if (!ar_block_barrier(a, b, 0, target)) {
+    fail_out();
+    return;
+  }
   if (!TWO_SHOT) {
     for (long long i = tid8; i < a.elems; i += stride)
       *reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.out) + i) = ar_sum8<T>(a, i);
@@ -197,7 +222,10 @@ allreduce_kernel(const AllReduceArgs a) {
       *reinterpret_cast<uint4*>(reinterpret_cast<T*>(a.res[a.rank]) + i) = ar_sum8<T>(a, i);
     __syncthreads();  // the release in the barrier below is cumulative over the block's result stores
     const int target1 = a.epoch[kArMaxBlocks + b] + 1;  // the second bank only advances in two-shot calls
-    ar_block_barrier(a, b, 1, target1);
+    if (!ar_block_barrier(a, b, 1, target1)) {
+      fail_out();
+      return;
+    }
     if (threadIdx.x == 0) a.epoch[kArMaxBlocks + b] = target1;
     for (int w = 0; w < a.world; ++w) {
       const long long wlo = slice * w;

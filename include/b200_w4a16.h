@@ -152,7 +152,10 @@ int b200_w4a16_dense_linear_forward(const void* input, const void* weight, const
  *   peer_in[w]   HOST array of `world` device pointers: rank w's symmetric input buffer T[elems], mapped
  *                into this process (e.g. torch.distributed._symmetric_memory buffer_ptrs)
  *   peer_sig[w]  HOST array of `world` device pointers: rank w's signal pad, int32[2][128][8], zero-initialised
- *   epoch        local device int32[2][128], zero-initialised, private to this (buffer, signal pad) pair
+ *   epoch        local device int32[2 * 128 + 1], zero-initialised, private to this (buffer, signal pad) pair; the
+ *                last int is a sticky ERROR word: a peer that does not arrive within 2 s (a rank died, or never
+ *                launched) sets it to 1, the output of the call is filled with NaN and the barrier state is left
+ *                untouched — a late or dead peer is an error the host can read, never a silently wrong sum
  *   out          local T[elems]; elems a multiple of 8
  * Every rank must call it the same number of times in the same order; callers alternate between two
  * (input buffer) sets so that no trailing barrier is needed.  Graph-capturable. */

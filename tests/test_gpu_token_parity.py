@@ -67,7 +67,7 @@ class _OurArm:
         import cpmcu_b200 as B
         self.B = B
         self.ws = torch.zeros(B.workspace_ints(2 * INTER), dtype=torch.int32, device=DEV)
-        self.ct = torch.empty(max(B.reduce_bytes(m, n, k) for _, k, n in SHAPES) // 4 + 64, dtype=torch.float32,
+        self.ct = torch.empty(max(B.reduce_bytes_fast(m, n, k) for _, k, n in SHAPES) // 4 + 64, dtype=torch.float32,
                               device=DEV)
 
     def linear(self, x, w):

@@ -25,7 +25,7 @@ ap.add_argument("--only", default="", help="chain only this shape (qkv|o|gate_up
 args = ap.parse_args()
 dev = "cuda"
 m = args.m
-ALL = list(range(1, 400)) + list(range(1001, 1040)) + list(range(2001, 2100))
+ALL = list(range(1, 400)) + list(range(1001, 1040))
 
 
 def resolve(x):
@@ -33,11 +33,6 @@ def resolve(x):
         return 0
     if x.isdigit():
         return int(x)
-    if "/S" in x and x.startswith("st/"):
-        name, S = x.rsplit("/S", 1)
-        for c in range(2001, 2100):
-            if L.config_name(c) == name and 1 + ((c - 2001) & 7) == int(S):
-                return c
     return next(c for c in ALL if x in (L.config_name(c) or ""))
 
 
@@ -52,7 +47,7 @@ for li in range(args.layers):
 acts = {k: torch.randn((m, k), device=dev).half() for k in (4096, 16384)}
 outs = {n: torch.empty((m, n), dtype=torch.float16, device=dev) for n in (4608, 4096, 32768)}
 ws = torch.zeros(B.workspace_ints(32768), dtype=torch.int32, device=dev)
-ct = torch.empty(max(B.reduce_bytes(m, n, k) for _, k, n in SHAPES) // 4 + 64, dtype=torch.float32, device=dev)
+ct = torch.empty(max(B.reduce_bytes_fast(m, n, k) for _, k, n in SHAPES) // 4 + 64, dtype=torch.float32, device=dev)
 total_bytes = sum(k * n // 2 + (k // 128) * n * 2 for _, k, n, _, _ in lay)
 
 for combo in (args.combo or [""]):

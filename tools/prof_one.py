@@ -22,7 +22,7 @@ a_ = ap.parse_args()
 dev = "cuda"
 if a_.cfg_name:
     from cpmcu_b200 import capi as _L
-    a_.cfg = next(c for c in list(range(1, 400)) + list(range(2001, 2100)) if a_.cfg_name in (_L.config_name(c) or ""))
+    a_.cfg = next(c for c in list(range(1, 400)) if a_.cfg_name in (_L.config_name(c) or ""))
     print("cfg", a_.cfg, _L.config_name(a_.cfg))
 k, n, m = a_.k, a_.n, a_.m
 qw = torch.randint(-2**31, 2**31 - 1, (a_.copies, k // 16, 2 * n), dtype=torch.int32, device=dev)
@@ -30,7 +30,7 @@ sc = (torch.rand((a_.copies, k // 128, n), device=dev) * 0.018 + 0.002).half()
 a = torch.randn((m, k), device=dev).half()
 out = torch.empty((m, n), dtype=torch.float16, device=dev)
 ws = torch.zeros(B.workspace_ints(n), dtype=torch.int32, device=dev)
-ct = torch.empty(max(B.reduce_bytes(m, n, k) // 4, 64), dtype=torch.float32, device=dev)
+ct = torch.empty(max(B.reduce_bytes_fast(m, n, k) // 4, 64), dtype=torch.float32, device=dev)
 for rep in range(2):
     for i in range(a_.copies):
         B.gemm(a, qw[i], sc[i], ws, ct, out=out, force_config=a_.cfg, pdl=a_.pdl)

@@ -20,7 +20,7 @@ for (m, k, n) in SHAPES:
     a = torch.randn((m, k), device=dev, generator=g).half()
     a2 = torch.randn((7, k), device=dev, generator=g).half()
     ws = torch.zeros(B.workspace_ints(n), dtype=torch.int32, device=dev)
-    ct = torch.empty(max(B.reduce_bytes(m, n, k), B.reduce_bytes(7, n, k), 4) // 4 + 64, dtype=torch.float32, device=dev)
+    ct = torch.empty(max(B.reduce_bytes_fast(m, n, k), B.reduce_bytes_fast(7, n, k), 4) // 4 + 64, dtype=torch.float32, device=dev)
     ref = B.gemm(a, qw, sc, ws, ct).clone()
     out = torch.empty_like(ref)
     bad = 0

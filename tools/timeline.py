@@ -25,7 +25,7 @@ ap.add_argument("--cfg-name", default="")
 args = ap.parse_args()
 dev = "cuda"
 if args.cfg_name:
-    args.cfg = next(c for c in list(range(1, 400)) + list(range(2001, 2100)) if args.cfg_name in (L.config_name(c) or ""))
+    args.cfg = next(c for c in list(range(1, 400)) if args.cfg_name in (L.config_name(c) or ""))
     print("cfg", args.cfg, L.config_name(args.cfg))
 names = args.shapes.split(",")
 m = args.m

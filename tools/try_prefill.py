@@ -25,7 +25,7 @@ def problem(m, k, n, dtype, seed=0):
 def check(m, k, n, dtype, cfg):
     a, qw, sc = problem(m, k, n, dtype, seed=m + n)
     ws = torch.zeros(B.workspace_ints(n), dtype=torch.int32, device=DEV)
-    ct = torch.empty(max(B.reduce_bytes(min(m, 64), n, k) // 4, 1), dtype=torch.float32, device=DEV)
+    ct = torch.empty(max(B.reduce_bytes_fast(min(m, 64), n, k) // 4, 1), dtype=torch.float32, device=DEV)
     out = B.gemm(a, qw, sc, ws, ct, force_config=cfg)
     torch.cuda.synchronize()
     w = B.dequant(qw, sc, k, n)
