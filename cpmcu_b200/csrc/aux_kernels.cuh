@@ -20,21 +20,18 @@ w4a16_dequant_kernel(const uint4* __restrict__ qweight, const T* __restrict__ sc
   for (long long blk = warp0; blk < blocks; blk += nwarps) {
     const int r = static_cast<int>(blk / chunks), ch = static_cast<int>(blk % chunks);
     const uint4 qv = qweight[blk * 32 + lane];
-    uint32_t s_lo[4] = {0, 0, 0, 0}, s_hi[4] = {0, 0, 0, 0};
+    uint32_t sc[4] = {0, 0, 0, 0};
     if (GROUPED) {
       const int grp = (r * 16) / group_size;
       const uint4 sv = *reinterpret_cast<const uint4*>(scales + static_cast<size_t>(grp) * n +
                                                        ch * 64 + g * 8);
-      broadcast_scale_pair(sv.x, s_lo[0], s_hi[0]);
-      broadcast_scale_pair(sv.y, s_lo[1], s_hi[1]);
-      broadcast_scale_pair(sv.z, s_lo[2], s_hi[2]);
-      broadcast_scale_pair(sv.w, s_lo[3], s_hi[3]);
+      sc[0] = sv.x; sc[1] = sv.y; sc[2] = sv.z; sc[3] = sv.w;
     }
     const uint32_t qq[4] = {qv.x, qv.y, qv.z, qv.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       uint32_t w[4];
-      Dequant<T>::template word<GROUPED>(qq[j], s_lo[j], s_hi[j], w);
+      Dequant<T>::template word<GROUPED>(qq[j], sc[j], w);
       // w[0]: (k 2t,2t+1 | n g)   w[1]: (k 2t,2t+1 | n g+8)   w[2]: (k 2t+8,+9 | n g)   w[3]: (.. | n g+8)
 #pragma unroll
       for (int e = 0; e < 4; ++e) {

@@ -335,10 +335,10 @@ struct Dequant;
 
 template <>
 struct Dequant<__half> {
-  // s_lo / s_hi: the group scale of column g / g+8, broadcast to both halves
+  // sc = {scale of column g (low half), scale of column g+8 (high half)}: the compiler folds the two broadcasts
+  // into the .H0_H0 / .H1_H1 operand modifiers of HMUL2 (no PRMT, one register per scale pair)
   template <bool SCALED>
-  static __device__ __forceinline__ void word(uint32_t q, uint32_t s_lo, uint32_t s_hi,
-                                              uint32_t (&w)[4]) {
+  static __device__ __forceinline__ void word(uint32_t q, uint32_t sc, uint32_t (&w)[4]) {
     constexpr uint32_t LO = 0x000f000f, HI = 0x00f000f0, EX = 0x64006400;
     constexpr uint32_t SUB = 0x64086408;  // 1032 = 1024 + 8
     constexpr uint32_t MUL = 0x2c002c00;  // 1/16
@@ -353,10 +353,11 @@ struct Dequant<__half> {
     __half2 v1 = __hsub2(as_h2(lo1), as_h2(SUB));
     __half2 v3 = __hfma2(as_h2(hi1), as_h2(MUL), as_h2(ADD));
     if (SCALED) {
-      v0 = __hmul2(v0, as_h2(s_lo));
-      v2 = __hmul2(v2, as_h2(s_lo));
-      v1 = __hmul2(v1, as_h2(s_hi));
-      v3 = __hmul2(v3, as_h2(s_hi));
+      const __half2 s_lo = __low2half2(as_h2(sc)), s_hi = __high2half2(as_h2(sc));
+      v0 = __hmul2(v0, s_lo);
+      v2 = __hmul2(v2, s_lo);
+      v1 = __hmul2(v1, s_hi);
+      v3 = __hmul2(v3, s_hi);
     }
     w[0] = as_u32(v0);
     w[1] = as_u32(v1);
@@ -374,8 +375,7 @@ struct Dequant<__half> {
 template <>
 struct Dequant<__nv_bfloat16> {
   template <bool SCALED>
-  static __device__ __forceinline__ void word(uint32_t q, uint32_t s_lo, uint32_t s_hi,
-                                              uint32_t (&w)[4]) {
+  static __device__ __forceinline__ void word(uint32_t q, uint32_t sc, uint32_t (&w)[4]) {
     constexpr uint32_t MASK = 0x000f000f, EX = 0x43004300;  // 128 + q, ulp(128) = 1
     constexpr uint32_t ONE = 0x3f803f80;                    // 1.0
     constexpr uint32_t ADD = 0xc308c308;                    // -136 = -(128 + 8)
@@ -388,10 +388,11 @@ struct Dequant<__nv_bfloat16> {
     __nv_bfloat162 v1 = __hfma2(as_b2(lo1), as_b2(ONE), as_b2(ADD));
     __nv_bfloat162 v3 = __hfma2(as_b2(hi1), as_b2(ONE), as_b2(ADD));
     if (SCALED) {
-      v0 = __hmul2(v0, as_b2(s_lo));
-      v2 = __hmul2(v2, as_b2(s_lo));
-      v1 = __hmul2(v1, as_b2(s_hi));
-      v3 = __hmul2(v3, as_b2(s_hi));
+      const __nv_bfloat162 s_lo = __low2bfloat162(as_b2(sc)), s_hi = __high2bfloat162(as_b2(sc));
+      v0 = __hmul2(v0, s_lo);
+      v2 = __hmul2(v2, s_lo);
+      v1 = __hmul2(v1, s_hi);
+      v3 = __hmul2(v3, s_hi);
     }
     w[0] = as_u32(v0);
     w[1] = as_u32(v1);
@@ -407,12 +408,7 @@ struct Dequant<__nv_bfloat16> {
 };
 
 // A lane's 16 bytes of a 64-column scale chunk are 8 scales for columns g + 8*jj, jj = 0..7
-// (gptq2marlin.py:55-57), i.e. word j = {s[16j+g], s[16j+g+8]}.  Split a word into the two
-// broadcast pairs dequant_word wants.
-__device__ __forceinline__ void broadcast_scale_pair(uint32_t s, uint32_t& s_lo, uint32_t& s_hi) {
-  s_lo = __byte_perm(s, 0, 0x1010);
-  s_hi = __byte_perm(s, 0, 0x3232);
-}
+// (gptq2marlin.py:55-57), i.e. word j = {s[16j+g], s[16j+g+8]}: exactly the pair Dequant<T>::word takes.
 
 // inverse of SCALE_PERM_SINGLE (gptq2marlin.py:58-60): position of column (n % 32) inside its
 // 32-column block of a channelwise (group_size == -1) scale row

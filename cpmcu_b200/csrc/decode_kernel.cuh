@@ -46,7 +46,12 @@ struct DecodeArgs {
   int colpar;     // 1: CTAs take whole columns (no split columns, no reduction through c_tmp)
   int gated;      // 1: tile = [TN/2 gate columns | the same TN/2 up columns]; c[M][N/2] = silu(gate) * up
   unsigned long long* dbg_ts;  // tuning only: per-CTA phase timestamps or null
+  int lab;                     // B200_DECODE_LAB builds only (experiments; wrong results): 1 = activations fetched for the
+                               // first ring fill only, 2 = scales likewise, 4 = consumers skip the dequant + MMA stream
 };
+#ifndef B200_DECODE_LAB
+#define B200_DECODE_LAB 0
+#endif
 
 __device__ __forceinline__ void dbg_stamp1(const DecodeArgs& p, int slot) {
   if (p.dbg_ts != nullptr && blockIdx.x < 1024) {
@@ -75,10 +80,13 @@ struct DecodeCfg {
   // ring depth: STAGES for M <= 8; one / two fewer for the wider token tiles, whose activation boxes and
   // reduction tile are bigger, so that the CTA stays under half an SM's shared memory (PDL co-residency)
   static constexpr int NSTAGE = (NT == 1) ? STAGES : ((NT == 2 ? STAGES - 1 : STAGES - 2) < 2 ? 2 : (NT == 2 ? STAGES - 1 : STAGES - 2));
-  static constexpr int OFF_A = 0;
-  static constexpr int OFF_W = OFF_A + NSTAGE * A_STAGE;
-  static constexpr int OFF_S = OFF_W + NSTAGE * W_STAGE;
-  static constexpr int OFF_RED = (OFF_S + NSTAGE * S_STAGE + 127) / 128 * 128;
+  // ring layout: one contiguous block per stage, [activations | int4 words | scales], so that a consumer needs ONE
+  // running stage pointer (every other offset is an immediate of the shared-memory instruction)
+  static constexpr int ST_A = 0;                     // 1024-aligned: 128B-swizzled boxes
+  static constexpr int ST_W = ST_A + A_STAGE;
+  static constexpr int ST_S = ST_W + W_STAGE;
+  static constexpr int STAGE_BYTES = (ST_S + S_STAGE + 1023) / 1024 * 1024;
+  static constexpr int OFF_RED = NSTAGE * STAGE_BYTES;
   static constexpr int OFF_BAR = OFF_RED + RED_BYTES;
   static constexpr int OFF_TK = OFF_BAR + (2 * NSTAGE + 2) * 8;  // two ticket broadcast words (flusher, consumers)
   static constexpr int SMEM_BYTES = OFF_TK + 16;
@@ -88,7 +96,7 @@ struct DecodeCfg {
   static constexpr int FLAGS_PER_TILE = CHUNKS * 16;  // ints of `workspace` owned by one column tile
   static_assert(WARPS % CHUNKS == 0 && KROWS % WK == 0, "warp layout");
   static_assert(KB % 64 == 0 && (KB <= 128 || (KB % 128 == 0 && 8 % WK == 0)), "stage k: a multiple of the 128-byte activation row; one group, or whole groups whose 8 k16-rows fall to one row index i of every warp");
-  static_assert(A_SUB % 1024 == 0 && W_STAGE % 1024 == 0, "TMA swizzle alignment");
+  static_assert(A_SUB % 1024 == 0 && W_STAGE % 128 == 0, "TMA swizzle / box alignment");
 };
 
 // unit partition helpers (64-bit: units * grid can exceed 2^31)
@@ -223,13 +231,16 @@ __device__ __forceinline__ void finish_segment(const DecodeArgs& p, const float*
     float* mine = cs.slots + static_cast<size_t>(cs.my_slot) * cs.slot_elems;
     for (int e = tid; e < items; e += nthr) __stcg(reinterpret_cast<float4*>(mine) + e, own_item(e));
   }
-  __threadfence();   // every writer: its stores are visible device-wide before the ticket below is drawn
-  sync();
-  if (tid == 0) *tk = atomicAdd(cs.counter, 1);
+  sync();   // the group's stores are ordered before thread 0's release below (cumulativity over the barrier)
+  if (tid == 0) {
+    int t;   // release: the partial is visible before the ticket; acquire: the earlier sharers' partials are visible after it
+    asm volatile("atom.add.acq_rel.gpu.global.s32 %0, [%1], 1;" : "=r"(t) : "l"(cs.counter) : "memory");
+    *tk = t;
+    if (nthr > 32) dbg_stamp1(p, 4);
+  }
   sync();
   if (*tk != cs.nparts - 1) return;   // somebody else arrives later and finishes the column
-  // ---- last arriver: every other partial is visible (their fences precede their tickets) ----
-  __threadfence();
+  // ---- last arriver: every other partial is visible (released before the other tickets, acquired with ours) ----
   if (tid == 0) *cs.counter = 0;      // all sharers have drawn: the workspace goes back to zero (reference contract)
   const int np1 = cs.nparts - 1;
   if (stage == nullptr || cap < np1 * (GATED ? RI : 1)) {
@@ -273,8 +284,11 @@ __device__ __forceinline__ void finish_segment(const DecodeArgs& p, const float*
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + e * 16), "l"(src + e) : "memory");
       ++row;
     }
-    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (tid == 0 && nthr > 32) dbg_stamp1(p, 5);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     sync();
+    if (tid == 0 && nthr > 32) dbg_stamp1(p, 6);
     auto sum_item = [&](int e) {   // e: item index inside the round
       float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int sl = 0, row = 0; sl < cs.nparts; ++sl) {   // slot order: bit-deterministic
@@ -308,6 +322,43 @@ __device__ __forceinline__ void finish_segment(const DecodeArgs& p, const float*
     sync();
   }
 }
+
+// A CTA's contiguous unit range [u0, u1) cut into column segments, walked in the order
+//     [partial END of its first column] [partial START of its last column] [its whole columns ...]
+// The partial segments are the ones other CTAs share: doing them FIRST means their split-column reduction
+// (publish, ticket, the last arriver's sum) happens in the flusher warp while every consumer streams on; what a
+// CTA finishes with is a whole column whenever it owns one, which needs no other CTA — the kernel's tail is then a
+// plain epilogue instead of a cross-CTA round trip.  The ticket scheme has no ordering requirement, so any walk
+// order is valid.
+struct SegWalk {
+  int kblks, c0, c1;   // first / last column of the range
+  int bf, bl;          // first k-block in c0, one past the last k-block in c1
+  int head, tail;      // 1: the range begins / ends inside a column (and c0 != c1)
+  int nseg;
+  __device__ __forceinline__ SegWalk(int u0, int u1, int kb) : kblks(kb) {
+    c0 = u0 / kb;
+    bf = u0 - c0 * kb;
+    c1 = (u1 - 1) / kb;
+    bl = (u1 - 1) - c1 * kb + 1;
+    if (c0 == c1) {
+      head = tail = 0;
+      nseg = 1;
+    } else {
+      head = bf != 0;
+      tail = bl != kb;
+      nseg = c1 - c0 + 1;
+    }
+  }
+  // i-th segment of the walk: column c, k-blocks [b0, b1)
+  __device__ __forceinline__ void get(int i, int& c, int& b0, int& b1) const {
+    if (c0 == c1) { c = c0; b0 = bf; b1 = bl; return; }
+    if (head && i == 0) { c = c0; b0 = bf; b1 = kblks; return; }
+    if (tail && i == head) { c = c1; b0 = 0; b1 = bl; return; }
+    c = c0 + head + (i - head - tail);   // whole columns, ascending
+    b0 = 0;
+    b1 = kblks;
+  }
+};
 
 // GATED: the fused [gate | up] tile + SiLU(gate) * up epilogue; a template parameter (not a runtime flag) so
 // that the plain kernels keep their register allocation and code exactly (a runtime flag cost 2 % at M <= 8)
@@ -368,53 +419,81 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       tma_prefetch_desc(&tm_w);
       tma_prefetch_desc(&tm_a);
       if (GROUPED) tma_prefetch_desc(&tm_s);
-      const int c0 = u0 / p.kblks, b0 = u0 - c0 * p.kblks;
+#if B200_DECODE_LAB
+      bool lab_first = true;   // still inside the first ring fill
+#endif
       auto issue_w = [&](int s, int c, int b) {
         const uint32_t full = bar_full + 8 * s;
+#if B200_DECODE_LAB
+        const bool skip_s = (p.lab & 2) && !lab_first, skip_a = (p.lab & 1) && !lab_first;
+        mbar_arrive_expect_tx(full, Cfg::STAGE_TX - (skip_s ? Cfg::S_STAGE : 0) - (skip_a ? Cfg::A_STAGE : 0));
+#else
         mbar_arrive_expect_tx(full, Cfg::STAGE_TX);
+#endif
         if (GATED) {  // one 4-d box: CHUNKS/2 gate chunks + the same CHUNKS/2 up chunks (see launch_decode)
-          tma_load_4d(sbase + Cfg::OFF_W + s * Cfg::W_STAGE, &tm_w, full, 0, c * (CHUNKS / 2), 0, b * KROWS,
+          tma_load_4d(sbase + s * Cfg::STAGE_BYTES + Cfg::ST_W, &tm_w, full, 0, c * (CHUNKS / 2), 0, b * KROWS,
                       kEvictFirst);
-          if (GROUPED)
-            tma_load_4d(sbase + Cfg::OFF_S + s * Cfg::S_STAGE, &tm_s, full, 0, c * (CHUNKS / 2), 0,
+          if (GROUPED
+#if B200_DECODE_LAB
+              && !skip_s
+#endif
+          )
+            tma_load_4d(sbase + s * Cfg::STAGE_BYTES + Cfg::ST_S, &tm_s, full, 0, c * (CHUNKS / 2), 0,
                         (b * KB) / 128, kEvictLast);
         } else {
-          tma_load_3d(sbase + Cfg::OFF_W + s * Cfg::W_STAGE, &tm_w, full, 0, c * CHUNKS, b * KROWS,
+          tma_load_3d(sbase + s * Cfg::STAGE_BYTES + Cfg::ST_W, &tm_w, full, 0, c * CHUNKS, b * KROWS,
                       kEvictFirst);
-          if (GROUPED)
-            tma_load_3d(sbase + Cfg::OFF_S + s * Cfg::S_STAGE, &tm_s, full, 0, c * CHUNKS,
+          if (GROUPED
+#if B200_DECODE_LAB
+              && !skip_s
+#endif
+          )
+            tma_load_3d(sbase + s * Cfg::STAGE_BYTES + Cfg::ST_S, &tm_s, full, 0, c * CHUNKS,
                         (b * KB) / 128, kEvictLast);
         }
       };
       auto issue_a = [&](int s, int b) {
         const uint32_t full = bar_full + 8 * s;
+#if B200_DECODE_LAB
+        if ((p.lab & 1) && !lab_first) return;
+#endif
 #pragma unroll
         for (int kc = 0; kc < KC; ++kc)
-          tma_load_2d(sbase + Cfg::OFF_A + s * Cfg::A_STAGE + kc * Cfg::A_SUB, &tm_a, full,
+          tma_load_2d(sbase + s * Cfg::STAGE_BYTES + Cfg::ST_A + kc * Cfg::A_SUB, &tm_a, full,
                       b * KB + kc * 64, 0, kEvictLast);
       };
+      const SegWalk walk(u0, u1, p.kblks);
       const int npre = my_units < NS ? my_units : NS;
-      int c = c0, b = b0;
-      for (int it = 0; it < npre; ++it) {   // weights do not depend on the prior grid
+      // weights do not depend on the prior grid: the first ring fill is requested before griddepcontrol.wait
+      int si = 0, c, b, bend;
+      walk.get(0, c, b, bend);
+      auto advance = [&]() {
+        if (++b == bend && si + 1 < walk.nseg) walk.get(++si, c, b, bend);
+      };
+      for (int it = 0; it < npre; ++it) {
         issue_w(it, c, b);
-        if (++b == p.kblks) { b = 0; ++c; }
+        advance();
       }
       pdl_wait_prior_grids();               // activations do
       dbg_stamp1(p, 1);
       {
-        int bb = b0;
+        int sj = 0, cc, bb, be;
+        walk.get(0, cc, bb, be);
         for (int it = 0; it < npre; ++it) {
           issue_a(it, bb);
-          if (++bb == p.kblks) bb = 0;
+          if (++bb == be && sj + 1 < walk.nseg) walk.get(++sj, cc, bb, be);
         }
       }
       int s = npre % NS;
       uint32_t ph = (npre == NS) ? 0u : 1u;  // parity of the empty-barrier phase to wait for
+#if B200_DECODE_LAB
+      lab_first = false;
+#endif
       for (int it = npre; it < my_units; ++it) {
         mbar_wait(bar_empty + 8 * s, ph);
         issue_w(s, c, b);
         issue_a(s, b);
-        if (++b == p.kblks) { b = 0; ++c; }
+        advance();
         if (++s == NS) { s = 0; ph ^= 1u; }
       }
     }
@@ -425,21 +504,15 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
     // ======================================= flusher =======================================
     // walks the same column segments as the consumers and finishes all but the CTA's last one
     pdl_wait_prior_grids();  // C, c_tmp and the counters are shared with prior grids
-    int u = u0;
-    uint32_t seg = 0;
-    while (true) {
-      const int c = u / p.kblks;
-      const int b_first = u - c * p.kblks;
-      const int col_end = (c + 1) * p.kblks;
-      const int uend = u1 < col_end ? u1 : col_end;
-      if (uend == u1) break;  // the CTA's last segment is finished by the consumer warps themselves
-      mbar_wait_backoff(bar_red_full, seg & 1u, 64);
-      finish_segment<T, TN, TNP, Cfg::FLAGS_PER_TILE, GROUPED, GATED>(p, red, c, /*whole=*/b_first == 0, units, grid,
-                                                                       lane, 32, WarpSync(), tk, nullptr, 0);
+    const SegWalk walk(u0, u1, p.kblks);
+    for (int si = 0; si + 1 < walk.nseg; ++si) {   // the CTA's last segment is finished by the consumer warps themselves
+      int c, b0, b1;
+      walk.get(si, c, b0, b1);
+      mbar_wait_backoff(bar_red_full, static_cast<uint32_t>(si) & 1u, 64);
+      finish_segment<T, TN, TNP, Cfg::FLAGS_PER_TILE, GROUPED, GATED>(p, red, c, /*whole=*/b0 == 0 && b1 == p.kblks, units,
+                                                                       grid, lane, 32, WarpSync(), tk, nullptr, 0);
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_red_empty);
-      u = uend;
-      ++seg;
     }
     return;
   }
@@ -471,46 +544,59 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
                                                 ((((wk & 3) << 1) ^ lm_half ^ (lm_row & 7)) << 4));
   const uint32_t s_off = static_cast<uint32_t>(wn * 128 + g * 16);
 
-  int b = u0 % p.kblks;   // k-block of the current unit inside its column
-  uint32_t seg = 0;       // column segments flushed so far
+  const SegWalk walk(u0, u1, p.kblks);
   int s = 0;
   uint32_t ph = 0;
+  uint32_t stg = sbase;        // running pointers: current stage block, its full / empty barriers
+  uint32_t bfull = bar_full, bempty = bar_empty;
+  // per-lane offsets inside a stage block (lane constants): the int4 words, the scales, the activation rows of the
+  // two swizzle phases this warp's rows alternate between
+  const uint32_t q_off = Cfg::ST_W + q_lane;
+  const uint32_t sc_off = Cfg::ST_S + s_off;
+  // row RI = WK * i of the stage: swizzle phase (RI & 3) << 1 XOR-ed into the 16-byte chunk index, sub-tile RI >> 2;
+  // loop-invariant, so computed once (equal values share a register)
+  uint32_t a_off[RPW];
+#pragma unroll
+  for (int i = 0; i < RPW; ++i) {
+    const int RI = WK * i;
+    a_off[i] = Cfg::ST_A + (a_lane ^ static_cast<uint32_t>(((RI & 3) << 1) << 4)) + static_cast<uint32_t>((RI >> 2) * Cfg::A_SUB);
+  }
 
   mbar_wait_backoff(bar_full, 0, 64);  // under PDL this first wait spans the tail of the previous kernel
   if (threadIdx.x == 0) dbg_stamp1(p, 2);
 
-  for (int it = 0; it < my_units; ++it) {
-    mbar_wait(bar_full + 8 * s, ph);
+  for (int si = 0; si < walk.nseg; ++si) {
+   int seg_c, seg_b0, seg_b1;
+   walk.get(si, seg_c, seg_b0, seg_b1);
+   for (int ub = seg_b0; ub < seg_b1; ++ub) {
+    mbar_wait(bfull, ph);
 
     // scales of the stage's groups: held for the whole stage when there are at most two, else fetched as
-    // each warp's row index i enters a new group (fewer live registers)
+    // each warp's row index i enters a new group (fewer live registers).  One register per {column g, g + 8} pair.
     constexpr bool LAZY_S = Cfg::SG > 2 && NT > 1;
     constexpr int SGL = LAZY_S ? 1 : Cfg::SG;
-    uint32_t s_lo[SGL][4], s_hi[SGL][4];
+    uint32_t sc[SGL][4];
     auto load_scales = [&](int slot, int gi) {
-      const uint4 sv = lds128(sbase + Cfg::OFF_S + s * Cfg::S_STAGE + gi * (TN * 2) + s_off);
-      broadcast_scale_pair(sv.x, s_lo[slot][0], s_hi[slot][0]);
-      broadcast_scale_pair(sv.y, s_lo[slot][1], s_hi[slot][1]);
-      broadcast_scale_pair(sv.z, s_lo[slot][2], s_hi[slot][2]);
-      broadcast_scale_pair(sv.w, s_lo[slot][3], s_hi[slot][3]);
+      const uint4 sv = lds128(stg + sc_off + gi * (TN * 2));
+      sc[slot][0] = sv.x; sc[slot][1] = sv.y; sc[slot][2] = sv.z; sc[slot][3] = sv.w;
     };
     if (GROUPED && !LAZY_S) {
 #pragma unroll
       for (int gi = 0; gi < Cfg::SG; ++gi) load_scales(gi, gi);
     }
-    const uint32_t wst = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
-    const uint32_t ast = sbase + Cfg::OFF_A + s * Cfg::A_STAGE;
 
     uint4 q[RPW];
 #pragma unroll
-    for (int i = 0; i < RPW; ++i) q[i] = lds128(wst + q_lane + i * (WARPS * 512));
+    for (int i = 0; i < RPW; ++i) q[i] = lds128(stg + q_off + i * (WARPS * 512));
+#if B200_DECODE_LAB
+    if (!(p.lab & 4))
+#endif
 #pragma unroll
     for (int i = 0; i < RPW; ++i) {
       // activation fragments: tokens as the N side of the MMA
       uint32_t bf[NT][2];
       const int RI = WK * i;  // compile-time after unrolling
-      const uint32_t a_row = ast + ((a_lane ^ static_cast<uint32_t>(((RI & 3) << 1) << 4)) +
-                                    static_cast<uint32_t>((RI >> 2) * Cfg::A_SUB));
+      const uint32_t a_row = stg + a_off[i];
       if (NT == 1) {
         ldmatrix_x2(bf[0][0], bf[0][1], a_row);
       } else {
@@ -524,18 +610,28 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
       for (int j = 0; j < 4; ++j) {
         uint32_t w[4];
         const int gi = (Cfg::SG > 1 && !LAZY_S) ? (RI >> 3) : 0;  // rows 8.. of a multi-group stage use the next scale rows
-        Dequant<T>::template word<GROUPED>(qq[j], s_lo[gi][j], s_hi[gi][j], w);
+        Dequant<T>::template word<GROUPED>(qq[j], GROUPED ? sc[gi][j] : 0u, w);
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) mma_m16n8k16<T>(acc[j][nt], w, bf[nt][0], bf[nt][1]);
       }
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive(bar_empty + 8 * s);
-    if (++s == NS) { s = 0; ph ^= 1u; }
+    if (lane == 0) mbar_arrive(bempty);
+    stg += Cfg::STAGE_BYTES;
+    bfull += 8;
+    bempty += 8;
+    if (++s == NS) {
+      s = 0;
+      ph ^= 1u;
+      stg = sbase;
+      bfull = bar_full;
+      bempty = bar_empty;
+    }
 
-    // ---- end of this CTA's run inside the column?  hand the tile over ----
-    if (b == p.kblks - 1 || it == my_units - 1) {
-      mbar_wait(bar_red_empty, (seg & 1u) ^ 1u);  // previous tile consumed (passes the first time)
+   }
+    // ---- the segment is complete: reduce the WK warps of every chunk into one tile, hand it over ----
+    {
+      mbar_wait(bar_red_empty, (static_cast<uint32_t>(si) & 1u) ^ 1u);  // previous tile consumed (passes the first time)
       // the WK warps sharing a chunk add their partials in wk order (fixed -> deterministic)
 #pragma unroll
       for (int r = 0; r < WK; ++r) {
@@ -557,27 +653,20 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
         }
         if (r + 1 < WK) named_bar_sync(1, NCONS);
       }
-      if (it == my_units - 1) {
-        // last segment of this CTA: nothing left to overlap with -> all consumer warps finish it; the weight
-        // ring is dead by now (every stage consumed) and serves as the staging area of the reduction
+      if (si == walk.nseg - 1) {
+        // last segment of this CTA: nothing left to overlap with -> all consumer warps finish it; the ring is dead
+        // by now (every stage consumed) and serves as the staging area of the reduction
         if (threadIdx.x == 0) dbg_stamp1(p, 3);
         named_bar_sync(1, NCONS);
         pdl_wait_prior_grids();  // C, c_tmp and the counters are shared with prior grids
-        const int c_last = (u1 - 1) / p.kblks;
-        const bool whole = (b == p.kblks - 1) && (u0 <= c_last * p.kblks);  // the segment spans the whole column
-        if (threadIdx.x == 0) dbg_stamp1(p, 5);
         finish_segment<T, TN, TNP, Cfg::FLAGS_PER_TILE, GROUPED, GATED>(
-            p, red, c_last, whole, units, grid, static_cast<int>(threadIdx.x), NCONS, ConsumerSync<NCONS>(), tk + 1,
-            reinterpret_cast<float4*>(smem + Cfg::OFF_W), (NS * Cfg::W_STAGE) / 16);
+            p, red, seg_c, /*whole=*/seg_b0 == 0 && seg_b1 == p.kblks, units, grid, static_cast<int>(threadIdx.x), NCONS,
+            ConsumerSync<NCONS>(), tk + 1, reinterpret_cast<float4*>(smem), (NS * Cfg::STAGE_BYTES) / 16);
         if (threadIdx.x == 0) dbg_stamp1(p, 7);
       } else {
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_red_full);
       }
-      ++seg;
-      b = 0;
-    } else {
-      ++b;
     }
   }
 }

@@ -242,13 +242,10 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
     uint32_t qph = 0, wph = 1;  // parities: raw slot filled; W slot drained (passes the first lap)
     for (int it = grp; it < total_its; it += Cfg::DGROUPS) {
       mbar_wait(bar_q_full + 8 * sq, qph);
-      uint32_t s_lo[4] = {0, 0, 0, 0}, s_hi[4] = {0, 0, 0, 0};
+      uint32_t sc[4] = {0, 0, 0, 0};
       if (GROUPED) {
         const uint4 sv = lds128(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE + s_lane);
-        broadcast_scale_pair(sv.x, s_lo[0], s_hi[0]);
-        broadcast_scale_pair(sv.y, s_lo[1], s_hi[1]);
-        broadcast_scale_pair(sv.z, s_lo[2], s_hi[2]);
-        broadcast_scale_pair(sv.w, s_lo[3], s_hi[3]);
+        sc[0] = sv.x; sc[1] = sv.y; sc[2] = sv.z; sc[3] = sv.w;
       }
       uint4 q[Cfg::RPW];
 #pragma unroll
@@ -263,7 +260,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint32_t w[4];
-            Dequant<T>::template word<GROUPED>(qq[j], s_lo[j], s_hi[j], w);
+            Dequant<T>::template word<GROUPED>(qq[j], sc[j], w);
             // w[0]: n=g, k 0..7 | w[1]: n=g+8, k 0..7 | w[2]: n=g, k 8..15 | w[3]: n=g+8, k 8..15
             stmatrix_x4(row_addr + j * 2048, w[0], w[1], w[2], w[3]);
           }

@@ -249,7 +249,12 @@ DecodePlan plan_decode(int mm, int n, int k, int geom, long long capacity, bool 
     pl->slot_max = 1;
     pl->need_bytes = 0;
   };
-  const int g0 = geom >= 0 ? geom : ((k % 128) == 0 ? 0 : 1);
+  // default geometry, measured on B200 (profiles/r02/decode_geometry_*.txt): the 256-column x 128-k stage has the fewest
+  // instructions per byte; for M > 8 on shapes with few column tiles (N <= ~9000: qkv, o, down) a 256-column tile is shared
+  // by 8+ CTAs and the last arriver of a column pulls 8 x M x 1 KB — the 128-column x 256-k stage halves both
+  int g0 = (k % 128) == 0 ? 0 : 1;
+  if (geom < 0 && !gated && mm > 8 && (k % 256) == 0 && ((n + 255) / 256) * 2 < sms) g0 = 5;
+  if (geom >= 0) g0 = geom;
   DecodePlan best;
   bool have = stream_k(g0, &best);
   if (have && best.grid == full_grid(best)) return best;

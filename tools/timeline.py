@@ -67,7 +67,7 @@ with torch.cuda.stream(s):
     s.synchronize()
 ts = buf.cpu().numpy().reshape(nl, 1024, 8)
 prev_end = None
-PH = ["start", "priorDone", "1stFull", "loopEnd", "ctaRed", "clSync", "stored", "exit"]
+PH = ["start", "priorDone", "1stFull", "loopEnd", "ticket", "tailWait", "fetched", "exit"]
 print("times in us relative to the launch's first CTA start; med/max over CTAs")
 print(f"{'launch':14s} {'ctas':>5s} {'gap':>6s} {'span':>6s} | " + " ".join(f"{p:>13s}" for p in PH))
 for i, (nm, k, n, _, _) in enumerate(lay):
