@@ -7,7 +7,9 @@ and two-shot reduction, launched from a CUDA graph and replayed.  Checks, per ca
   * column-parallel: the rank's output equals the matching columns of the UNSHARDED b200_w4a16_gemm (tolerance: the
     split-K order of the two launches differs);
   * row-parallel: all-reduced output within tolerance of the unsharded GEMM and of the exact product (fp64 matmul of
-    the library's bit-exact dequant), BIT-IDENTICAL on every rank and from replay to replay;
+    the library's bit-exact dequant) — max floored relative error <= 1e-2 for fp16, <= 3e-2 for bf16 (the partials
+    are rounded to T before the fp32 sum: W + 1 roundings of an 8-bit significand) — BIT-IDENTICAL on every rank and
+    from replay to replay;
   * a peer that never calls the collective produces an ERROR on the waiting rank (error word + NaN output), not a sum.
 """
 import os
@@ -17,7 +19,7 @@ import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
-TOL = 1e-2
+TOL = {torch.float16: 1e-2, torch.bfloat16: 3e-2}   # bf16 carries 8 significand bits: W rounded partials + one more rounding
 
 
 def _free_port():
@@ -66,7 +68,7 @@ def _worker(rank, world, port, results):
                     ct = torch.empty(B.reduce_bytes_fast(m, n, k) // 4 + 64, dtype=torch.float32, device=dev)
                     full = B.gemm(a, q, s, ws, ct, stream=stream)
                     exact = a.double() @ w64
-                    assert _rel(full, exact) <= TOL
+                    assert _rel(full, exact) <= TOL[tdt]
                     if style == "col":
                         loc = B.gemm(a, ql, sl, ws, ct, stream=stream)
                         cols, off = [], 0
@@ -77,7 +79,7 @@ def _worker(rank, world, port, results):
                         want = torch.cat(cols, dim=1)
                         stream.synchronize()
                         r = _rel(loc, want)
-                        assert r <= TOL, (name, m, tdt, r)
+                        assert r <= TOL[tdt], (name, m, tdt, r)
                         log.append((name, str(tdt), m, "col", r))
                         continue
                     al = a[:, k0:k1].contiguous()
@@ -107,7 +109,7 @@ def _worker(rank, world, port, results):
                         assert all(torch.equal(gathered[0], t) for t in gathered), (name, m, tdt, two_shot, "ranks differ")
                         r_full, r_exact = _rel(out, full), _rel(out, exact)
                         # W fp16/bf16-rounded partials are summed in fp32: W roundings instead of one
-                        assert r_exact <= TOL and r_full <= TOL, (name, m, tdt, two_shot, r_full, r_exact)
+                        assert r_exact <= TOL[tdt] and r_full <= TOL[tdt], (name, m, tdt, two_shot, r_full, r_exact)
                         assert int(ws.abs().max()) == 0
                         log.append((name, str(tdt), m, "two-shot" if two_shot else "one-shot", r_exact))
                         del gr
