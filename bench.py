@@ -216,7 +216,7 @@ def main():
     ap.add_argument("--no-tp1", action="store_true", help="skip the unsharded Llama-3-70B record (the tp = 1 base of the scaling curve)")
     ap.add_argument("--workload", default="auto", choices=["auto", "minicpm4", "llama70b"],
                     help="auto: MiniCPM4-8B linears at N=1, tensor-parallel Llama-3-70B linears at N>1")
-    ap.add_argument("--collective", default="oneshot", choices=["oneshot", "nccl"],
+    ap.add_argument("--collective", default="fused", choices=["fused", "oneshot", "nccl"],
                     help="all-reduce after the row-parallel linears (N > 1): this library's one-shot NVLink kernel, or NCCL")
     ap.add_argument("--tp-layers", type=int, default=16)
     ap.add_argument("--tp-widths", default="1,16,64")

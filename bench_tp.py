@@ -138,7 +138,7 @@ def measure_tp(args, torch, dev, dist, rank, world, local_rank, use_reference=Fa
     collective = "none"
     if eff_world > 1:
         collective = "NCCL all-reduce (fp16, sum) inside the CUDA graph"
-        if getattr(args, "collective", "oneshot") == "oneshot":
+        if getattr(args, "collective", "fused") in ("oneshot", "fused"):
             try:
                 from cpmcu_b200.collective import OneShotAllReduce
                 ar = OneShotAllReduce(max(widths) * max(d["n"] for d in lins if d["style"] == "row"),
@@ -152,6 +152,13 @@ def measure_tp(args, torch, dev, dist, rank, world, local_rank, use_reference=Fa
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)   # every rank must take the same path
         if int(flag.item()) == 0:
             ar, collective = None, "NCCL all-reduce (fp16, sum) inside the CUDA graph"
+    # the all-reduce fused into the row-parallel GEMM launch (M <= 32); wider steps keep the separate collective
+    fused = None
+    if eff_world > 1 and not use_reference and getattr(args, "collective", "fused") == "fused":
+        from cpmcu_b200.collective import FusedRowParallel
+        fused = FusedRowParallel(32 * max(d["n"] for d in lins if d["style"] == "row"), torch.float16, dev)
+        collective = ("M <= 32: all-reduce fused into the row-parallel GEMM launch (b200_w4a16_gemm_ar: tiles pushed to "
+                      "every peer over NVLink, reduced locally in rank order); M > 32: " + collective)
     tp_check = None
     if eff_world > 1 and not use_reference:
         tp_check = check_tp_result(torch, dist, dev, eff_world, eff_rank, widths, ar, stream)
@@ -169,6 +176,10 @@ def measure_tp(args, torch, dev, dist, rank, world, local_rank, use_reference=Fa
         for l in range(L):
             for i, d in enumerate(lins):
                 reduce_here = comm and d["style"] == "row" and eff_world > 1
+                if reduce_here and fused is not None and m <= 32 and compute:
+                    fused.gemm(acts[m][i], d["q"][l], d["s"][l], d["ws"], c_tmp, outs[m][i], pdl=not args.no_pdl, stream=stream)
+                    n_launch[0] += 1
+                    continue
                 if reduce_here and ar is not None:
                     buf = ar.next_input(m, d["n"])      # the GEMM writes its partial into the symmetric buffer
                     if compute:
@@ -249,6 +260,8 @@ def measure_tp(args, torch, dev, dist, rank, world, local_rank, use_reference=Fa
         e2e_step()
     e2e_ms = timed(e2e_step, K)
     clocks = sampler.stop()
+    if fused is not None:
+        fused.check()
     if ar is not None:
         ar.check()   # a peer that never arrived is an error (NaN output + error word), never a silently wrong sum
     if eff_world > 1:

@@ -22,6 +22,18 @@ class B200W4A16Error(RuntimeError):
     pass
 
 
+class FusedAR(ctypes.Structure):
+    """b200_w4a16_ar: buffers of the all-reduce fused into a row-parallel GEMM launch"""
+    _fields_ = [
+        ("recv", c_void_p),
+        ("flag", c_void_p),
+        ("seen", c_void_p),
+        ("slot_elems", c_int64),
+        ("rank", c_int),
+        ("world", c_int),
+    ]
+
+
 class Opts(ctypes.Structure):
     _fields_ = [
         ("bias", c_void_p),
@@ -49,6 +61,8 @@ SYMBOLS = {
     "b200_w4a16_gemm_ex": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                    c_void_p, POINTER(Opts)]),
+    "b200_w4a16_gemm_ar": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int,
+                                   c_void_p, c_void_p, POINTER(Opts), POINTER(FusedAR)]),
     "b200_w4a16_linear_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_int, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p,
                                           c_void_p]),

@@ -92,3 +92,80 @@ class OneShotAllReduce:
             _l._raise(rc)
         self._turn ^= 1
         return out
+
+
+AR_TILES = 1024
+
+
+class FusedRowParallel:
+    """Row-parallel W4A16 linear with the all-reduce fused into the GEMM launch (`b200_w4a16_gemm_ar`, M <= 32):
+
+        fr = FusedRowParallel(max_elems=32 * 8192, dtype=torch.float16, device=dev)
+        fr.gemm(a_local, qweight_rows, scales_rows, workspace, c_tmp, out)   # out[m, n] = sum over ranks, same bits on all
+
+    torch.distributed's symmetric-memory allocator provides the peer-mapped receive buffers and counters; the data
+    movement and the reduction are this library's kernel.  Every rank must issue the same sequence of calls."""
+
+    def __init__(self, max_elems: int, dtype, device, group=None):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        if not 2 <= self.world <= MAX_WORLD:
+            raise ValueError(f"FusedRowParallel needs 2..{MAX_WORLD} ranks")
+        gname = self.group.group_name
+        if hasattr(symm, "enable_symm_mem_for_group"):
+            import warnings
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                try:
+                    symm.enable_symm_mem_for_group(gname)
+                except Exception:  # noqa: BLE001
+                    pass
+        self.slot_elems = (max_elems + 7) // 8 * 8
+        self.dtype, self.device = dtype, device
+        self.recv = symm.empty((2 * self.world * self.slot_elems,), dtype=dtype, device=device)
+        self.flag = symm.empty((self.world * AR_TILES,), dtype=torch.int32, device=device)
+        self.recv.zero_()
+        self.flag.zero_()
+        torch.cuda.synchronize(device)
+        hr = symm.rendezvous(self.recv, gname)
+        hf = symm.rendezvous(self.flag, gname)
+        dist.barrier(self.group)
+        PtrArr = ctypes.c_void_p * self.world
+        self._recv = PtrArr(*[int(p) for p in hr.buffer_ptrs])
+        self._flag = PtrArr(*[int(p) for p in hf.buffer_ptrs])
+        self.seen = torch.zeros(AR_TILES + 8, dtype=torch.int32, device=device)
+        self._handles = (hr, hf)
+        self._ar = _l.FusedAR()
+        self._ar.recv = ctypes.cast(self._recv, ctypes.c_void_p)
+        self._ar.flag = ctypes.cast(self._flag, ctypes.c_void_p)
+        self._ar.seen = self.seen.data_ptr()
+        self._ar.slot_elems = self.slot_elems
+        self._ar.rank, self._ar.world = self.rank, self.world
+
+    def gemm(self, a, qweight, scales, workspace, c_tmp, out, *, group_size=128, bias=None, residual=None,
+             out_scale=0.0, pdl=False, stream=None):
+        m, k = a.shape
+        n = qweight.shape[1] // 2
+        assert m * n <= self.slot_elems and out.shape == (m, n)
+        o = _l.Opts()
+        o.bias = None if bias is None else bias.data_ptr()
+        o.residual = None if residual is None else residual.data_ptr()
+        o.c_tmp_bytes = 0 if c_tmp is None else c_tmp.numel() * c_tmp.element_size()
+        o.out_scale = float(out_scale)
+        o.pdl = 1 if pdl else 0
+        rc = _l.lib().b200_w4a16_gemm_ar(_l._ptr(a), _l._ptr(qweight), _l._ptr(scales), _l._ptr(workspace), _l._ptr(out),
+                                         m, n, k, group_size, _l.dtype_code(a.dtype), _l._ptr(c_tmp), _l._stream(stream),
+                                         ctypes.byref(o), ctypes.byref(self._ar))
+        if rc:
+            _l._raise(rc)
+        return out
+
+    def check(self):
+        """raises if a source rank failed to deliver a tile within 2 s in any call so far (device sync)"""
+        import torch
+        torch.cuda.synchronize(self.device)
+        if int(self.seen[AR_TILES].item()) != 0:
+            raise RuntimeError(f"fused all-reduce: a source rank of rank {self.rank} did not deliver within 2 s")

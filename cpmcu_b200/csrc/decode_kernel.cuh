@@ -45,6 +45,12 @@ struct DecodeArgs {
   int slot_max;   // slots per column reserved in c_tmp
   int colpar;     // 1: CTAs take whole columns (no split columns, no reduction through c_tmp)
   int gated;      // 1: tile = [TN/2 gate columns | the same TN/2 up columns]; c[M][N/2] = silu(gate) * up
+  // fused all-reduce of a row-parallel linear over NVLink peer memory (ar_world > 1; see the "fused all-reduce" block)
+  void* ar_recv[8];            // rank w's receive buffer T[2 parities][world sources][ar_slot_elems], peer-mapped
+  int* ar_flag[8];             // rank w's arrival counters int[world sources][kArTiles], monotonic, peer-mapped
+  int* ar_seen;                // local int[kArTiles + 1]: epochs consumed per column tile; last int = sticky error word
+  long long ar_slot_elems;
+  int ar_world, ar_rank;
   unsigned long long* dbg_ts;  // tuning only: per-CTA phase timestamps or null
   int lab;                     // B200_DECODE_LAB builds only (experiments; wrong results): 1 = activations fetched for the
                                // first ring fill only, 2 = scales likewise, 4 = consumers skip the dequant + MMA stream
@@ -52,6 +58,46 @@ struct DecodeArgs {
 #ifndef B200_DECODE_LAB
 #define B200_DECODE_LAB 0
 #endif
+constexpr int kArTiles = 1024;   // column tiles a fused all-reduce can track (N <= 64 * 1024)
+
+// ---- fused all-reduce (tensor-parallel row-parallel linears: o, down) ----------------------------------------
+// The CTA that completes a column tile (whole owner or last ticket holder) does not write C: it rounds the tile to T
+// and PUSHES it into every rank's receive buffer (slot = its own rank, buffer parity = the tile's epoch), then raises
+// that tile's counter on every rank with a system-scope release.  After its last unit every CTA turns reducer for the
+// tiles c = blockIdx.x, blockIdx.x + grid, ...: it waits for the world counters of the tile (pushes from OTHER GPUs
+// and from local CTAs that never wait on anything themselves, so this cannot deadlock), adds the world partials out of
+// LOCAL memory in rank order in fp32 (bit-identical on every rank), applies the epilogue and writes C.  One launch: the
+// transfer of early tiles overlaps the rest of the stream, there is no separate collective kernel and no grid barrier.
+// Two buffer parities suffice: a rank can only be one call ahead of a peer (its call i+1 completes only after the
+// peer's pushes of call i+1, which follow the peer's whole call i in stream order).
+__device__ __forceinline__ int ld_acquire_sys_s32(const int* p) {
+  int v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_relaxed_sys_u4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+// push 4 fp32 sums of (tok, columns n..n+3), rounded to T (channelwise: scaled as the reference scales the rounded sum),
+// into slot `rank` of every peer's receive buffer
+template <typename T, bool GROUPED>
+__device__ __forceinline__ void ar_push(const DecodeArgs& p, int parity, int tok, int n, float4 v) {
+  T o[4] = {Elem<T>::from_float(v.x), Elem<T>::from_float(v.y), Elem<T>::from_float(v.z), Elem<T>::from_float(v.w)};
+  if (!GROUPED) {
+    const T* sc = reinterpret_cast<const T*>(p.scales);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o[e] = __hmul(o[e], sc[chan_scale_pos(n + e)]);
+  }
+  uint2 pk;
+  pk.x = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[0])) | (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[1])) << 16);
+  pk.y = static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[2])) | (static_cast<uint32_t>(*reinterpret_cast<uint16_t*>(&o[3])) << 16);
+  const size_t off = (static_cast<size_t>(parity) * p.ar_world + p.ar_rank) * p.ar_slot_elems + static_cast<size_t>(tok) * p.n + n;
+#pragma unroll
+  for (int w = 0; w < 8; ++w)
+    if (w < p.ar_world) *reinterpret_cast<uint2*>(reinterpret_cast<T*>(p.ar_recv[w]) + off) = pk;
+}
 
 __device__ __forceinline__ void dbg_stamp1(const DecodeArgs& p, int slot) {
   if (p.dbg_ts != nullptr && blockIdx.x < 1024) {
@@ -211,6 +257,19 @@ __device__ __forceinline__ void finish_segment(const DecodeArgs& p, const float*
     const int tok = item / RI, nn = (item - tok * RI) * 4;
     return *reinterpret_cast<const float4*>(red + tok * TNP + nn);
   };
+  // fused all-reduce: the finished tile goes to every rank's receive buffer instead of C (see ar_push)
+  const bool ar = !GATED && p.ar_world > 1;
+  const int ar_parity = ar ? ((p.ar_seen[c] + 1) & 1) : 0;
+  auto emit = [&](int tok, int n, float4 v) {
+    if (ar) ar_push<T, GROUPED>(p, ar_parity, tok, n, v);
+    else emit_out<T, GROUPED>(p, tok, n, v);
+  };
+  auto ar_signal = [&]() {   // called by the whole group after the tile has been pushed
+    if (!ar) return;
+    sync();   // the group's pushes are ordered before the releases below
+    if (tid < p.ar_world)
+      asm volatile("red.release.sys.global.add.s32 [%0], 1;" ::"l"(p.ar_flag[tid] + p.ar_rank * kArTiles + c) : "memory");
+  };
   if (whole) {
     if (GATED) {
       for (int e = tid; e < p.m * (RI / 2); e += nthr) {
@@ -220,9 +279,10 @@ __device__ __forceinline__ void finish_segment(const DecodeArgs& p, const float*
     } else {
       for (int e = tid; e < items; e += nthr) {
         const int tok = e / RI, nn = (e - tok * RI) * 4;
-        if (col0 + nn < p.n) emit_out<T, GROUPED>(p, tok, col0 + nn, own_item(e));
+        if (col0 + nn < p.n) emit(tok, col0 + nn, own_item(e));
       }
     }
+    ar_signal();
     return;
   }
   const ColumnShare cs = column_share<TN, FLAGS_PER_TILE>(p, c, units, grid);
@@ -266,9 +326,10 @@ __device__ __forceinline__ void finish_segment(const DecodeArgs& p, const float*
     } else {
       for (int e = tid; e < items; e += nthr) {
         const int tok = e / RI, nn = (e - tok * RI) * 4;
-        if (col0 + nn < p.n) emit_out<T, GROUPED>(p, tok, col0 + nn, sum_item(e));
+        if (col0 + nn < p.n) emit(tok, col0 + nn, sum_item(e));
       }
     }
+    ar_signal();
     return;
   }
   // staged: rounds of `ib` items; all copies of a round in flight at once (16-byte cp.async, L2 -> shared).
@@ -316,11 +377,12 @@ __device__ __forceinline__ void finish_segment(const DecodeArgs& p, const float*
       for (int e = tid; e < ni; e += nthr) {
         const int item = i0 + e;
         const int tok = item / RI, nn = (item - tok * RI) * 4;
-        if (col0 + nn < p.n) emit_out<T, GROUPED>(p, tok, col0 + nn, sum_item(e));
+        if (col0 + nn < p.n) emit(tok, col0 + nn, sum_item(e));
       }
     }
     sync();
   }
+  ar_signal();
 }
 
 // A CTA's contiguous unit range [u0, u1) cut into column segments, walked in the order
@@ -667,6 +729,50 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_red_full);
       }
+    }
+  }
+
+  // ---- fused all-reduce, second half: this CTA's share of the column tiles (see the block comment above) ----
+  if (!GATED && p.ar_world > 1) {
+    const int tid = static_cast<int>(threadIdx.x);
+    const T* recv = reinterpret_cast<const T*>(p.ar_recv[p.ar_rank]);
+    const int* flags = p.ar_flag[p.ar_rank];
+    for (int c = blockIdx.x; c < p.ncols; c += gridDim.x) {
+      const int target = p.ar_seen[c] + 1;
+      named_bar_sync(1, NCONS);   // everybody has read the epoch before anybody advances it
+      bool ok = true;
+      if (tid < p.ar_world) {
+        const int* f = flags + tid * kArTiles + c;
+        unsigned long long t0 = 0;
+        for (unsigned spin = 0; ld_acquire_sys_s32(f) - target < 0; ++spin) {
+          if ((spin & 1023u) == 1023u) {   // a source that is 2 s late is treated as dead: error word, no sum
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t0 == 0) t0 = t;
+            if (t - t0 > 2000000000ull) { ok = false; break; }
+          }
+        }
+        if (!ok) atomicExch(p.ar_seen + kArTiles, 1);
+      }
+      named_bar_sync(1, NCONS);
+      const size_t pbase = static_cast<size_t>(target & 1) * p.ar_world * p.ar_slot_elems;
+      const int col0 = c * TN;
+      for (int e = tid; e < p.m * (TN / 8); e += NCONS) {
+        const int tok = e / (TN / 8), n = col0 + (e - tok * (TN / 8)) * 8;
+        if (n >= p.n) continue;
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int w = 0; w < p.ar_world; ++w) {   // rank order: every rank computes the same bits
+          const uint4 v = ld_relaxed_sys_u4(recv + pbase + static_cast<size_t>(w) * p.ar_slot_elems + static_cast<size_t>(tok) * p.n + n);
+          const T* h = reinterpret_cast<const T*>(&v);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] += Elem<T>::to_float(h[i]);
+        }
+        // the partials already carry the channelwise scale (ar_push): the epilogue here is the grouped one
+        emit_out<T, true>(p, tok, n, make_float4(acc[0], acc[1], acc[2], acc[3]));
+        emit_out<T, true>(p, tok, n + 4, make_float4(acc[4], acc[5], acc[6], acc[7]));
+      }
+      named_bar_sync(1, NCONS);
+      if (tid == 0) p.ar_seen[c] = target;
     }
   }
 }

@@ -25,6 +25,12 @@ struct GemmCall {
   int dtype;
   bool pdl;
   cudaStream_t stream;
+  // fused all-reduce (b200_w4a16_gemm_ar): device pointers copied from the caller's host arrays; ar_world <= 1: off
+  void* ar_recv[8];
+  int* ar_flag[8];
+  int* ar_seen;
+  long long ar_slot_elems;
+  int ar_world, ar_rank;
 };
 
 // defined in w4a16_abi.cu

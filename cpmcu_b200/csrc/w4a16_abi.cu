@@ -405,10 +405,10 @@ const char* b200_w4a16_config_name(int config) {
   return decode_name(config);
 }
 
-int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales, const int32_t* g_idx,
-                       const int32_t* perm, int32_t* workspace, void* c, int64_t m, int64_t n, int64_t k,
-                       int group_size, int dtype, int is_k_full, int has_act_order, void* a_tmp,
-                       float* c_tmp, void* stream, const b200_w4a16_opts* opts) {
+static int gemm_impl(const void* a, const int32_t* qweight, const void* scales, const int32_t* g_idx,
+                     const int32_t* perm, int32_t* workspace, void* c, int64_t m, int64_t n, int64_t k,
+                     int group_size, int dtype, int is_k_full, int has_act_order, void* a_tmp,
+                     float* c_tmp, void* stream, const b200_w4a16_opts* opts, const b200_w4a16_ar* ar) {
   (void)g_idx;
   // ---- validation: the reference's checks (gptq_marlin.cu:71-72, gptq_marlin_mm.cu:53-54,84-131) ----
   if (!(m > 0 && n > 0 && k > 0))
@@ -481,6 +481,29 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
   g.dtype = dtype;
   g.pdl = opts ? (opts->pdl != 0) : (g_default_pdl.load(std::memory_order_relaxed) != 0);
   g.stream = st;
+  std::memset(g.ar_recv, 0, sizeof(g.ar_recv));
+  std::memset(g.ar_flag, 0, sizeof(g.ar_flag));
+  g.ar_seen = nullptr;
+  g.ar_slot_elems = 0;
+  g.ar_world = 1;
+  g.ar_rank = 0;
+  if (ar && ar->world > 1) {
+    if (ar->world > 8 || ar->rank < 0 || ar->rank >= ar->world)
+      return fail(B200_W4A16_EINVAL, "gemm_ar: world must be 2..8 and 0 <= rank < world (got %d, %d)", ar->world, ar->rank);
+    if (m > kStreamMaxM || forced >= kPrefillBase || gated || has_act_order)
+      return fail(B200_W4A16_EINVAL, "gemm_ar: the fused all-reduce serves M <= %d without gated_silu / act-order (got M = %lld)", kStreamMaxM, (long long)m);
+    if (!ar->recv || !ar->flag || !ar->seen || ar->slot_elems < m * n || ar->slot_elems % 8)
+      return fail(B200_W4A16_EINVAL, "gemm_ar: null buffers or slot_elems (%lld) smaller than m * n", (long long)ar->slot_elems);
+    for (int w = 0; w < ar->world; ++w) {
+      if (!ar->recv[w] || !ar->flag[w]) return fail(B200_W4A16_EINVAL, "gemm_ar: null peer pointer for rank %d", w);
+      g.ar_recv[w] = ar->recv[w];
+      g.ar_flag[w] = ar->flag[w];
+    }
+    g.ar_seen = ar->seen;
+    g.ar_slot_elems = ar->slot_elems;
+    g.ar_world = ar->world;
+    g.ar_rank = ar->rank;
+  }
   // ---- tensor-bound regime: one persistent tcgen05 launch for any M ----
   if ((forced == 0 && m > kStreamMaxM) || forced >= kPrefillBase) {
     if (forced >= kPrefillBase + kPrefillIds)
@@ -520,6 +543,22 @@ int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales
     if (int rc = (dtype == 0 ? launch_decode_fp16(s, pl, nt) : launch_decode_bf16(s, pl, nt))) return rc;
   }
   return B200_W4A16_OK;
+}
+
+int b200_w4a16_gemm_ex(const void* a, const int32_t* qweight, const void* scales, const int32_t* g_idx,
+                       const int32_t* perm, int32_t* workspace, void* c, int64_t m, int64_t n, int64_t k,
+                       int group_size, int dtype, int is_k_full, int has_act_order, void* a_tmp,
+                       float* c_tmp, void* stream, const b200_w4a16_opts* opts) {
+  return gemm_impl(a, qweight, scales, g_idx, perm, workspace, c, m, n, k, group_size, dtype, is_k_full, has_act_order,
+                   a_tmp, c_tmp, stream, opts, nullptr);
+}
+
+int b200_w4a16_gemm_ar(const void* a, const int32_t* qweight, const void* scales, int32_t* workspace, void* c,
+                       int64_t m, int64_t n, int64_t k, int group_size, int dtype, float* c_tmp, void* stream,
+                       const b200_w4a16_opts* opts, const b200_w4a16_ar* ar) {
+  if (!ar) return fail(B200_W4A16_EINVAL, "gemm_ar: ar is null");
+  return gemm_impl(a, qweight, scales, nullptr, nullptr, workspace, c, m, n, k, group_size, dtype, 1, 0, nullptr, c_tmp,
+                   stream, opts, ar);
 }
 
 int b200_w4a16_gemm(const void* a, const int32_t* qweight, const void* scales, const int32_t* g_idx,

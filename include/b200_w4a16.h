@@ -169,6 +169,29 @@ int b200_w4a16_allreduce(const void* const* peer_in, void* const* peer_res, int3
                          int32_t* epoch, void* out, int64_t elems, int dtype, int rank, int world,
                          int two_shot, void* stream);
 
+/* Row-parallel linear (o / down sharded along K) with the all-reduce FUSED into the GEMM launch (M <= 32, the
+ * streaming kernel): the CTA that completes a column tile pushes it, rounded to T, into every rank's receive buffer
+ * over NVLink and raises a per-tile counter; after its last unit every CTA reduces its share of the tiles out of LOCAL
+ * memory (fp32, rank order: bit-identical on every rank), applies the post-ops of `opts` and writes `c`.  No separate
+ * collective launch, no grid-wide barrier; early tiles travel while the rest of the weights stream.
+ *   recv[w]   HOST array of `world` device pointers: rank w's receive buffer, T[2][world][slot_elems] (symmetric
+ *             memory, e.g. torch.distributed._symmetric_memory), slot_elems >= m * n, a multiple of 8
+ *   flag[w]   HOST array of `world` device pointers: rank w's counters, int32[world][1024], zero-initialised once
+ *   seen      local int32[1025], zero-initialised once (epochs per column tile; the last int is a sticky error word set
+ *             when a source rank did not deliver within 2 s — the affected tiles are then not written)
+ * Every rank must make the same sequence of calls on the same (recv, flag, seen) set.  M > 32, gated_silu and
+ * act-order are value errors (use b200_w4a16_gemm_ex + b200_w4a16_allreduce there).  Graph-capturable. */
+typedef struct b200_w4a16_ar {
+  void* const* recv;
+  int32_t* const* flag;
+  int32_t* seen;
+  int64_t slot_elems;
+  int rank, world;
+} b200_w4a16_ar;
+int b200_w4a16_gemm_ar(const void* a, const int32_t* qweight, const void* scales, int32_t* workspace, void* c,
+                       int64_t m, int64_t n, int64_t k, int group_size, int dtype, float* c_tmp, void* stream,
+                       const b200_w4a16_opts* opts, const b200_w4a16_ar* ar);
+
 /* Process-wide default for programmatic dependent launch on entry points that take no opts
  * (b200_w4a16_gemm, b200_w4a16_linear_forward): 1 = every GEMM launch carries the PDL attribute so
  * its weight prefetch overlaps the tail of the previous kernel in the stream (safe with any

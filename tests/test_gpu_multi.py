@@ -41,7 +41,7 @@ def _worker(rank, world, port, results):
     import torch.distributed as dist
     import cpmcu_b200 as B
     from cpmcu_b200 import sharding as sh
-    from cpmcu_b200.collective import OneShotAllReduce
+    from cpmcu_b200.collective import FusedRowParallel, OneShotAllReduce
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", device_id=dev)
@@ -51,6 +51,7 @@ def _worker(rank, world, port, results):
         torch.cuda.set_stream(stream)
         for tdt in (torch.float16, torch.bfloat16):
             ar = OneShotAllReduce(64 * 8192, tdt, dev)
+            fr = FusedRowParallel(32 * 8192, tdt, dev)
             for name, k, n, style, parts in (("qkv", 8192, 10240, "col", [8192, 1024, 1024]),
                                              ("o", 8192, 8192, "row", None), ("down", 28672, 8192, "row", None)):
                 g = torch.Generator(device=dev).manual_seed(k + n)      # same seed everywhere: identical full tensors
@@ -83,6 +84,40 @@ def _worker(rank, world, port, results):
                         log.append((name, str(tdt), m, "col", r))
                         continue
                     al = a[:, k0:k1].contiguous()
+                    if m <= 32:
+                        # the all-reduce fused into the GEMM launch (b200_w4a16_gemm_ar): same checks, plus post-ops
+                        # applied AFTER the sum: RN(RN(res + sum) * T(scale)) on the fused result == on a plain one
+                        out = torch.empty((m, n), dtype=tdt, device=dev)
+
+                        def fstep():
+                            for _ in range(3):
+                                fr.gemm(al, ql, sl, ws, ct, out, pdl=True, stream=stream)
+                        fstep()
+                        stream.synchronize()
+                        gr = torch.cuda.CUDAGraph()
+                        with torch.cuda.graph(gr, stream=stream):
+                            fstep()
+                        gr.replay()
+                        stream.synchronize()
+                        first = out.clone()
+                        for _ in range(5):
+                            gr.replay()
+                        stream.synchronize()
+                        fr.check()
+                        assert torch.equal(first, out), (name, m, tdt, "fused: not repeatable")
+                        gathered = [torch.empty_like(out) for _ in range(world)]
+                        dist.all_gather(gathered, out)
+                        assert all(torch.equal(gathered[0], t) for t in gathered), (name, m, tdt, "fused: ranks differ")
+                        r_full, r_exact = _rel(out, full), _rel(out, exact)
+                        assert r_exact <= TOL[tdt] and r_full <= TOL[tdt], (name, m, tdt, "fused", r_full, r_exact)
+                        res = torch.randn((m, n), device=dev, generator=g).to(tdt)
+                        out2 = torch.empty_like(out)
+                        fr.gemm(al, ql, sl, ws, ct, out2, residual=res, out_scale=0.25, stream=stream)
+                        stream.synchronize()
+                        assert torch.equal(out2, (res + out) * torch.tensor(0.25, device=dev).to(tdt)), (name, m, tdt, "fused post-ops")
+                        assert int(ws.abs().max()) == 0
+                        log.append((name, str(tdt), m, "fused", r_exact))
+                        del gr
                     for two_shot in (False, True):
                         out = torch.empty((m, n), dtype=tdt, device=dev)
 
@@ -113,7 +148,7 @@ def _worker(rank, world, port, results):
                         assert int(ws.abs().max()) == 0
                         log.append((name, str(tdt), m, "two-shot" if two_shot else "one-shot", r_exact))
                         del gr
-            del ar
+            del ar, fr
         # ---- a peer that never arrives: error, not a wrong sum ----
         ar = OneShotAllReduce(8192, torch.float16, dev)
         dist.barrier()
@@ -158,5 +193,5 @@ def test_tensor_parallel_linears_and_nvlink_allreduce():
         status, payload = results[r]
         assert status == "ok", f"rank {r}:\n{payload}"
     cases = results[0][1]
-    assert len(cases) >= 2 * (3 + 2 * 3 * 2) + 1
+    assert len(cases) >= 2 * (3 + 2 * 3 * 2 + 2 * 2) + 1
     print("\n" + "\n".join(f"{c}" for c in cases))
