@@ -43,7 +43,9 @@ class Opts(ctypes.Structure):
         ("pdl", c_int),
         ("out_scale", c_float),
         ("gated_silu", c_int),
-        ("reserved", c_int * 3),
+        ("qkv_q_dim", c_int),
+        ("qkv_kv_dim", c_int),
+        ("reserved", c_int * 1),
     ]
 
 
@@ -177,8 +179,8 @@ def config_name(cfg: int) -> str:
 
 
 def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm=None, a_tmp=None,
-         bias=None, residual=None, out_scale=0.0, gated_silu=False, force_config=0, pdl=False,
-         stream=None):
+         bias=None, residual=None, out_scale=0.0, gated_silu=False, qkv_split=None, force_config=0,
+         pdl=False, stream=None):
     """C[M,N] = A[M,K] . dequant(qweight, scales)  (+ residual, + bias, * T(out_scale)) on the current stream.
 
     a: [M,K] fp16/bf16 cuda, qweight: int32 [K/16, 2N] cuda (Marlin), scales: [K/g, N] (Marlin-permuted),
@@ -197,6 +199,8 @@ def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm
     o.c_tmp_bytes = 0 if c_tmp is None else c_tmp.numel() * c_tmp.element_size()
     o.out_scale = float(out_scale)
     o.gated_silu = 1 if gated_silu else 0
+    if qkv_split is not None:   # (q_dim, kv_dim): c = [q: M x q_dim][k: M x kv_dim][v: M x kv_dim]
+        o.qkv_q_dim, o.qkv_kv_dim = int(qkv_split[0]), int(qkv_split[1])
     o.force_config = force_config
     o.pdl = 1 if pdl else 0
     rc = lib().b200_w4a16_gemm_ex(_ptr(a), _ptr(qweight), _ptr(scales), None, _ptr(perm), _ptr(workspace),

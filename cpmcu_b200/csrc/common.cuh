@@ -285,6 +285,16 @@ __device__ __forceinline__ T apply_out_scale(T o, uint32_t os) {
   return o;
 }
 
+// Output element offset.  qa == 0: row-major C[tok][n].  qa > 0 (opts.qkv_q_dim / qkv_kv_dim): the fused q|k|v
+// projection written SPLIT, [q: M x qa][k: M x qb][v: M x qb] — what the reference's permute kernel produces from the
+// row-major qkv output when M > 1 (src/model/attn.cuh:23-39,56-60; w4a16_gptq_marlin_attn.cuh:132), without the launch.
+__device__ __forceinline__ size_t out_offset(int tok, int n, int n_total, int m_total, int qa, int qb) {
+  if (qa == 0) return static_cast<size_t>(tok) * n_total + n;
+  if (n < qa) return static_cast<size_t>(tok) * qa + n;
+  if (n < qa + qb) return static_cast<size_t>(m_total) * qa + static_cast<size_t>(tok) * qb + (n - qa);
+  return static_cast<size_t>(m_total) * (qa + qb) + static_cast<size_t>(tok) * qb + (n - qa - qb);
+}
+
 // D(16x8,f32) += A(16x16,T,row) * B(16x8,T,col): the register-operand tensor path.  In the
 // HBM-bound regime the weights arrive as registers straight out of the dequantiser, which is the
 // one case where mma.sync (not tcgen05, whose operands live in shared/tensor memory) is the right

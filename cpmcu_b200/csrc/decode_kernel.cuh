@@ -45,6 +45,7 @@ struct DecodeArgs {
   int slot_max;   // slots per column reserved in c_tmp
   int colpar;     // 1: CTAs take whole columns (no split columns, no reduction through c_tmp)
   int gated;      // 1: tile = [TN/2 gate columns | the same TN/2 up columns]; c[M][N/2] = silu(gate) * up
+  int qkv_a, qkv_b;            // > 0: write the q | k | v column ranges split (out_offset, common.cuh); 0: row-major
   // fused all-reduce of a row-parallel linear over NVLink peer memory (ar_world > 1; see the "fused all-reduce" block)
   void* ar_recv[8];            // rank w's receive buffer T[2 parities][world sources][ar_slot_elems], peer-mapped
   int* ar_flag[8];             // rank w's arrival counters int[world sources][kArTiles], monotonic, peer-mapped
@@ -165,7 +166,7 @@ __device__ __forceinline__ void emit_out(const DecodeArgs& p, int tok, int n, fl
 #pragma unroll
     for (int e = 0; e < 4; ++e) o[e] = __hmul(o[e], sc[chan_scale_pos(n + e)]);
   }
-  const size_t off = static_cast<size_t>(tok) * p.n + n;
+  const size_t off = out_offset(tok, n, p.n, p.m, p.qkv_a, p.qkv_b);
   if (p.residual) {
     const T* rs = reinterpret_cast<const T*>(p.residual) + off;
 #pragma unroll

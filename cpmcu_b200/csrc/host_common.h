@@ -19,6 +19,7 @@ struct GemmCall {
   const void* bias;
   const void* residual;
   float out_scale;  // 0 = none
+  int qkv_a, qkv_b; // > 0: q | k | v written split (opts.qkv_q_dim / qkv_kv_dim)
   bool gated;       // fused SiLU(gate) * up epilogue over the [gate | up] columns
   int m, n, k;
   int group_size;

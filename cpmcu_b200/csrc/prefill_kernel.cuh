@@ -31,6 +31,7 @@ struct PrefillArgs {
   uint32_t out_scale;    // 0, or 0x10000 | bits of T(scale): last post-op
   int m, n, k;
   int n_tiles, m_tiles, kblks;
+  int qkv_a, qkv_b;      // > 0: q | k | v written split (out_offset, common.cuh)
 };
 
 template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT = false>
@@ -319,7 +320,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
               if (tok < p.m) {
                 T o = Elem<T>::from_float(__uint_as_float(v[i]));
                 if (!GROUPED) o = __hmul(o, chan_s);  // channelwise: scale the ROUNDED sum
-                const size_t off = static_cast<size_t>(tok) * p.n + n;
+                const size_t off = out_offset(tok, n, p.n, p.m, p.qkv_a, p.qkv_b);
                 if (rbase) o = __hadd(rbase[off], o);
                 if (p.bias) o = __hadd(o, bias_v);
                 o = apply_out_scale<T>(o, p.out_scale);
@@ -367,7 +368,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
           for (int i = 0; i < 4; ++i) o[i] = __hmul(o[i], sc[chan_scale_pos(n + i)]);
         }
-        const size_t goff = static_cast<size_t>(m0 + tok) * p.n + n;
+        const size_t goff = out_offset(m0 + tok, n, p.n, p.m, p.qkv_a, p.qkv_b);
         if (p.residual) {
           const T* rs = reinterpret_cast<const T*>(p.residual) + goff;
 #pragma unroll

@@ -463,7 +463,16 @@ static int gemm_impl(const void* a, const int32_t* qweight, const void* scales, 
       return fail(B200_W4A16_EINVAL, "gated_silu does not combine with bias / residual / out_scale");
     if (has_act_order) return fail(B200_W4A16_EINVAL, "gated_silu does not combine with act-order");
   }
+  const int qa = opts ? opts->qkv_q_dim : 0, qb = opts ? opts->qkv_kv_dim : 0;
+  if (qa || qb) {
+    if (qa <= 0 || qb <= 0 || qa % 8 || qb % 8 || qa + 2ll * qb != n)
+      return fail(B200_W4A16_EINVAL, "qkv split: need qkv_q_dim + 2 * qkv_kv_dim == N and both multiples of 8 (got %d, %d, N = %lld)", qa, qb, (long long)n);
+    if (gated || (opts && opts->residual) || (forced > 0 && forced < kPrefillBase && m > 32))
+      return fail(B200_W4A16_EINVAL, "qkv split does not combine with gated_silu / residual / a multi-slab forced launch");
+  }
   GemmCall g;
+  g.qkv_a = qa;
+  g.qkv_b = qb;
   g.a = a;
   g.qweight = qweight;
   g.scales = scales;

@@ -106,6 +106,8 @@ int launch_one(const GemmCall& g, int S, int* query) {
   args.n_tiles = (g.n + Cfg::BN - 1) / Cfg::BN;
   args.m_tiles = (g.m + BM - 1) / BM;
   args.kblks = g.k / 64;
+  args.qkv_a = g.qkv_a;
+  args.qkv_b = g.qkv_b;
   const long long tiles = static_cast<long long>(args.n_tiles) * args.m_tiles;
   int grid = static_cast<int>(tiles < sm_count() ? tiles : sm_count());
   if (SPLIT) {

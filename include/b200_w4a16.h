@@ -66,7 +66,13 @@ typedef struct b200_w4a16_opts {
    * error beyond, where the caller keeps the separate activation kernel.  Needs group_size 128 and
    * N % 256 == 0; does not combine with bias / residual / out_scale / act-order. */
   int gated_silu;
-  int reserved[3];
+  /* > 0: the weight is the fused q | k | v projection (N = qkv_q_dim + 2 * qkv_kv_dim) and `c` is written SPLIT,
+   * [q: M x qkv_q_dim][k: M x qkv_kv_dim][v: M x qkv_kv_dim] — the layout the reference's `permute` launch produces
+   * from the row-major output when M > 1 (src/model/attn.cuh:23-39,56-60; w4a16_gptq_marlin_attn.cuh:132) — so that
+   * launch and its staging buffer disappear.  Both multiples of 8; does not combine with residual / gated_silu. */
+  int qkv_q_dim;
+  int qkv_kv_dim;
+  int reserved[1];
 } b200_w4a16_opts;
 
 /* Replaces gptq_marlin_gemm<T> (src/qgemm/gptq_marlin/gptq_marlin.cuh:11-27, gptq_marlin.cu:42-86)

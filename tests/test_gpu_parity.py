@@ -553,3 +553,28 @@ def test_repack_gptq_on_device(case):
     got = L.repack_gptq(torch.from_numpy(np.ascontiguousarray(gptq)).to(DEV))
     torch.cuda.synchronize()
     assert np.array_equal(got.cpu().numpy().view(np.uint32), np.ascontiguousarray(want).view(np.uint32))
+
+
+@pytest.mark.parametrize("tdt", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("m", [1, 5, 16, 32, 40, 200, 600])
+def test_qkv_split_write(tdt, m):
+    """opts.qkv_q_dim / qkv_kv_dim: the fused q | k | v projection written as [q: M x a][k: M x b][v: M x b] — bit for
+    bit what the reference's permute launch (src/model/attn.cuh:23-39, called at w4a16_gptq_marlin_attn.cuh:132 when
+    num_tokens > 1) makes of the row-major output — on the streaming, tcgen05 split-K and tcgen05 whole-K kernels."""
+    b = _b()
+    k, qa, qb = 512, 384, 128           # 3 "heads" of 128 + 1 kv head of 128
+    n = qa + 2 * qb
+    dtype = mo.FP16 if tdt == torch.float16 else mo.BF16
+    prob = mo.make_problem(m, k, n, 128, dtype, seed=77 + m)
+    a, qw, sc = t_store(prob["a"], dtype), torch.from_numpy(prob["qweight"]).to(DEV), t_store(prob["scales_marlin"], dtype)
+    ws, c_tmp = scratch(m, n, k)
+    bias = torch.randn((n,), device=DEV).to(tdt)
+    plain = b.gemm(a, qw, sc, ws, c_tmp, bias=bias)
+    split = torch.empty(m * n, dtype=tdt, device=DEV)
+    b.gemm(a, qw, sc, ws, c_tmp, out=split.view(m, n), bias=bias, qkv_split=(qa, qb))
+    torch.cuda.synchronize()
+    want = torch.cat([plain[:, :qa].reshape(-1), plain[:, qa:qa + qb].reshape(-1), plain[:, qa + qb:].reshape(-1)])
+    assert torch.equal(split, want)
+    assert int(ws.abs().max()) == 0
+    with pytest.raises(ValueError):
+        b.gemm(a, qw, sc, ws, c_tmp, qkv_split=(qa, qb + 8))
