@@ -80,7 +80,8 @@ int launch_decode_fp16(const GemmCall& g, const DecodePlan& pl, int nt);
 int launch_decode_bf16(const GemmCall& g, const DecodePlan& pl, int nt);
 
 // defined in w4a16_prefill.cu: the tcgen05 regime
-constexpr int kPrefillTiles = 6;  // (NSUB,BM) = (2,256) (1,256) (2,128) (1,128); split-K (1,64) (1,128)
+constexpr int kPrefillTiles = 7;  // (NSUB,BM) = (2,256) (1,256) (2,128) (1,128); split-K (1,64) (1,128); CTA pair (256 cols, 256)
+constexpr int kPrefillPairTile = 6;
 constexpr int kPrefillWholeK = 4; // tiles below this index are whole-K (persistent); the rest are split-K
 void prefill_pick(const GemmCall& g, int* tile, int* S);
 const char* prefill_tile_name(int tile);

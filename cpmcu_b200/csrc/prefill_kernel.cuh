@@ -34,12 +34,17 @@ struct PrefillArgs {
   int qkv_a, qkv_b;      // > 0: q | k | v written split (out_offset, common.cuh)
 };
 
-template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT = false>
+// PAIR: cta_group::2 — a cluster of two CTAs works on 256 weight columns x BM tokens: each CTA dequantises its own 128
+// columns and stages HALF of the token tile, so the activation operand crosses the L2 -> SM fabric once per 256
+// columns instead of once per 128 (what bounds the single-CTA tiles) with the accumulator still double
+// buffered in each CTA's tensor memory.
+template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT = false, bool PAIR = false>
 struct PrefillCfg {
   static constexpr int BN = NSUB * 128;            // output columns per CTA tile
   static constexpr int CHUNKS = NSUB * 2;          // 64-column Marlin chunks per tile
   static constexpr int BK = 64;                    // k per stage = one 128-byte swizzled row
-  static constexpr int A_STAGE = BM * 128;         // activations  [BM][64] T
+  static constexpr int A_ROWS = PAIR ? BM / 2 : BM;  // token rows this CTA stages (PAIR: its half; the box is always A_ROWS tall)
+  static constexpr int A_STAGE = A_ROWS * 128;     // activations  [A_ROWS][64] T
   static constexpr int W_STAGE = BN * 128;         // dequantised  [BN][64] T
   static constexpr int Q_STAGE = 4 * CHUNKS * 512; // raw int4: 4 k16-rows x CHUNKS blocks of 512 B
   static constexpr int S_STAGE = GROUPED ? BN * 2 : 0;
@@ -70,15 +75,17 @@ struct PrefillCfg {
   static_assert(TMEM_COLS >= 32 && TMEM_COLS <= 512 && (TMEM_COLS & (TMEM_COLS - 1)) == 0, "tensor memory allocation");
   static_assert(!SPLIT || (NSUB == 1 && RED_BYTES <= OFF_BAR), "split-K staging must fit in the dead rings (A, W and Q are all drained when the accumulator is complete)");
   static_assert(BM % 16 == 0 && BM <= 256, "UMMA N");
+  static_assert(!PAIR || (NSUB == 1 && !SPLIT && BM % 32 == 0), "cta_group::2: one 128-row sub-tile per CTA, whole K");
   static_assert(SMEM_BYTES <= 232448, "shared memory budget (227 KB)");
 };
 
-template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT>
+template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT, bool PAIR = false>
 __global__ void __launch_bounds__((7 + DW) * 32, SPLIT ? 2 : 1)
 w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_s,
                      const __grid_constant__ CUtensorMap tm_a, const PrefillArgs p) {
-  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
+  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT, PAIR>;
   constexpr int CHUNKS = Cfg::CHUNKS;
+  const int prank = PAIR ? static_cast<int>(cluster_ctarank()) : 0;   // 0: leader (issues the UMMAs)
 
   // no static shared memory in this kernel: the dynamic window starts 1024-aligned (SWIZZLE_128B operand
   // tiles need it); checked, not assumed
@@ -103,7 +110,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(bar_a_full + 8 * s, 1);
-      mbar_init(bar_w_full + 8 * s, Cfg::DWG);
+      mbar_init(bar_w_full + 8 * s, PAIR ? 2 * Cfg::DWG : Cfg::DWG);   // PAIR: the peer's dequantisers arrive here too
       mbar_init(bar_consumed + 8 * s, 1);
     }
 #pragma unroll
@@ -114,13 +121,17 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
     for (int a = 0; a < 2; ++a) {
       mbar_init(bar_acc_full + 8 * a, 1);
-      mbar_init(bar_acc_empty + 8 * a, 4);
+      mbar_init(bar_acc_empty + 8 * a, PAIR ? 8 : 4);
     }
     fence_barrier_init();
   }
-  if (warp == 5) tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), Cfg::TMEM_COLS);
+  if (warp == 5) {
+    if (PAIR) tmem_alloc_pair(smem_u32(const_cast<uint32_t*>(tmem_slot)), Cfg::TMEM_COLS);
+    else tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), Cfg::TMEM_COLS);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();   // both CTAs' barriers are initialised before either one arrives remotely
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -133,6 +144,10 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
   // work items: persistent walk over whole-K tiles, or (split-K) exactly one tile and one K slice
   // per CTA, the S CTAs of a cluster sharing the tile
   int tile_begin = blockIdx.x, tile_step = gridDim.x, kb_lo = 0, kb_hi = p.kblks;
+  if (PAIR) {   // the two CTAs of a pair walk the same (256-column, token) tiles
+    tile_begin = blockIdx.x >> 1;
+    tile_step = gridDim.x >> 1;
+  }
   int csize = 1, crank = 0;
   if (SPLIT) {
     csize = static_cast<int>(cluster_nctarank());
@@ -154,9 +169,20 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
         for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
           const int s = it % STAGES;
           mbar_wait_backoff(bar_consumed + 8 * s, ((it / STAGES) & 1) ^ 1, 32);
-          mbar_arrive_expect_tx(bar_a_full + 8 * s, Cfg::A_STAGE);
-          tma_load_2d(sbase + Cfg::OFF_A + s * Cfg::A_STAGE, &tm_a, bar_a_full + 8 * s, kb * 64, mt * BM,
-                      kEvictLast);
+          if (PAIR) {
+            // tokens [m0 + rank * h, + h) with h = half of the tile's valid tokens rounded up to 16: the UMMA reads h rows
+            // from each CTA, so accumulator column j is token m0 + j for ragged tiles too
+            int vt = p.m - mt * BM;
+            vt = vt > BM ? BM : vt;
+            const int h = ((vt + 15) & ~15) >> 1;
+            if (prank == 0) mbar_arrive_expect_tx(bar_a_full + 8 * s, 2 * Cfg::A_STAGE);
+            tma_load_2d_pair(sbase + Cfg::OFF_A + s * Cfg::A_STAGE, &tm_a, bar_a_full + 8 * s, kb * 64, mt * BM + prank * h,
+                             kEvictLast);
+          } else {
+            mbar_arrive_expect_tx(bar_a_full + 8 * s, Cfg::A_STAGE);
+            tma_load_2d(sbase + Cfg::OFF_A + s * Cfg::A_STAGE, &tm_a, bar_a_full + 8 * s, kb * 64, mt * BM,
+                        kEvictLast);
+          }
         }
       }
     }
@@ -174,16 +200,18 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
           const int sq = it % QSTAGES;
           mbar_wait_backoff(bar_q_empty + 8 * sq, ((it / QSTAGES) & 1) ^ 1, 32);
           mbar_arrive_expect_tx(bar_q_full + 8 * sq, Cfg::Q_STAGE + Cfg::S_STAGE);
-          tma_load_3d(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE, &tm_w, bar_q_full + 8 * sq, 0, nt * CHUNKS,
+          const int ch0 = PAIR ? (2 * nt + prank) * CHUNKS : nt * CHUNKS;   // PAIR: nt counts 256-column tiles
+          tma_load_3d(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE, &tm_w, bar_q_full + 8 * sq, 0, ch0,
                       kb * 4, SPLIT ? kEvictFirst : kEvictNormal);
           if (GROUPED)
             tma_load_3d(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE, &tm_s, bar_q_full + 8 * sq, 0,
-                        nt * CHUNKS, kb >> 1, kEvictLast);
+                        ch0, kb >> 1, kEvictLast);
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 5 && prank == 0) {
     // ======================================= MMA issuer =======================================
+    // (PAIR: the leader CTA only; one instruction drives both SMs' tensor cores)
     int it = 0, acc_it = 0;
     for (int tile = tile_begin; tile < total_tiles; tile += tile_step, ++acc_it) {
       const int mt = tile % p.m_tiles;
@@ -192,7 +220,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       tc_fence_after();
       int vt = p.m - mt * BM;
       vt = vt > BM ? BM : vt;
-      const uint32_t idesc = umma_idesc_f16<T>(128, static_cast<uint32_t>((vt + 15) & ~15));
+      const uint32_t idesc = umma_idesc_f16<T>(PAIR ? 256 : 128, static_cast<uint32_t>((vt + 15) & ~15));
       const uint32_t d0 = tmem_base + acc * Cfg::ACC_COLS;
       for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
         const int s = it % STAGES;
@@ -209,11 +237,17 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
             for (int kk = 0; kk < 4; ++kk) {
               const uint64_t adesc = umma_desc_k_sw128(w_addr + sub * 16384 + kk * 32);
               const uint64_t bdesc = umma_desc_k_sw128(a_addr + kk * 32);
-              tc_mma_f16(d0 + sub * BM, adesc, bdesc, idesc, (kb != kb_lo || kk != 0) ? 1u : 0u);
+              if (PAIR) tc_mma_f16_pair(d0 + sub * BM, adesc, bdesc, idesc, (kb != kb_lo || kk != 0) ? 1u : 0u);
+              else tc_mma_f16(d0 + sub * BM, adesc, bdesc, idesc, (kb != kb_lo || kk != 0) ? 1u : 0u);
             }
           }
-          tc_commit(bar_consumed + 8 * s);
-          if (kb == kb_hi - 1) tc_commit(bar_acc_full + 8 * acc);
+          if (PAIR) {   // frees the A / W slots and publishes the accumulator in BOTH CTAs
+            tc_commit_pair(bar_consumed + 8 * s);
+            if (kb == kb_hi - 1) tc_commit_pair(bar_acc_full + 8 * acc);
+          } else {
+            tc_commit(bar_consumed + 8 * s);
+            if (kb == kb_hi - 1) tc_commit(bar_acc_full + 8 * acc);
+          }
         }
         __syncwarp();
       }
@@ -272,13 +306,16 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       // shared-memory loads are then complete by data dependence, not by an assumption about issue order
       // (releasing right after ISSUING the loads was the round-1 split-K race)
       if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);
-      if (lane == 0) mbar_arrive(bar_w_full + 8 * s);
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_leader(bar_w_full + 8 * s);   // the leader's issuer waits for both CTAs' halves of the W operand
+        else mbar_arrive(bar_w_full + 8 * s);
+      }
       sq += Cfg::DGROUPS;
       if (sq >= QSTAGES) { sq -= QSTAGES; qph ^= 1u; }
       s += Cfg::DGROUPS;
       if (s >= STAGES) { s -= STAGES; wph ^= 1u; }
     }
-  } else {
+  } else if (warp < 4) {
     // ======================================== epilogue ========================================
     const int qd = warp;  // TMEM lane quarter: this warp may touch lanes 32*qd .. 32*qd+31
     pdl_wait_prior_grids();
@@ -295,7 +332,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       const T* rbase = reinterpret_cast<const T*>(p.residual);
 #pragma unroll 1
       for (int sub = 0; sub < NSUB; ++sub) {
-        const int n = nt * Cfg::BN + sub * 128 + qd * 32 + lane;
+        const int n = (PAIR ? (2 * nt + prank) * 128 : nt * Cfg::BN + sub * 128) + qd * 32 + lane;
         const bool nok = n < p.n;
         T bias_v = Elem<T>::from_float(0.f), chan_s = Elem<T>::from_float(1.f);
         if (nok && p.bias) bias_v = reinterpret_cast<const T*>(p.bias)[n];
@@ -332,7 +369,10 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_acc_empty + 8 * acc);
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_leader(bar_acc_empty + 8 * acc);
+        else mbar_arrive(bar_acc_empty + 8 * acc);
+      }
     }
   }
 
@@ -394,8 +434,12 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 
   // teardown: every role is done with tensor memory before it is returned
   tc_fence_before();
-  __syncthreads();
-  if (warp == 5) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  if (PAIR) cluster_sync_all();   // neither CTA returns tensor memory or exits while the pair's UMMAs / arrives may be in flight
+  else __syncthreads();
+  if (warp == 5) {
+    if (PAIR) tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
+    else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
 }
 
 }  // namespace b200

@@ -249,11 +249,13 @@ DecodePlan plan_decode(int mm, int n, int k, int geom, long long capacity, bool 
     pl->slot_max = 1;
     pl->need_bytes = 0;
   };
-  // default geometry, measured on B200 (profiles/r02/decode_geometry_*.txt): the 256-column x 128-k stage has the fewest
-  // instructions per byte; for M > 8 on shapes with few column tiles (N <= ~9000: qkv, o, down) a 256-column tile is shared
-  // by 8+ CTAs and the last arriver of a column pulls 8 x M x 1 KB — the 128-column x 256-k stage halves both
+  // default geometry, measured on B200 (profiles/r02/c_decode_geometry_chains.txt, h_decode_m16_mixing.txt): the
+  // 256-column x 128-k stage has the fewest instructions per byte (M <= 8).  For M > 8 a 256-column tile of a small-N
+  // shape (qkv, o, down) is shared by 8+ CTAs and the last arriver of a column pulls 8 x M x 1 KB: the 128-column x 256-k
+  // stage halves both.  ONE geometry per token-block width for every shape: alternating between two kernel functions
+  // inside a layer costs more than the better per-shape choice gains (M = 16: 74 us per layer mixed, 67 us uniform).
   int g0 = (k % 128) == 0 ? 0 : 1;
-  if (geom < 0 && !gated && mm > 8 && (k % 256) == 0 && ((n + 255) / 256) * 2 < sms) g0 = 5;
+  if (geom < 0 && !gated && mm > 8 && (k % 256) == 0) g0 = 5;
   if (geom >= 0) g0 = geom;
   DecodePlan best;
   bool have = stream_k(g0, &best);
@@ -295,11 +297,13 @@ const char* decode_name(int id) {
 }
 
 constexpr int kPrefillBase = 1001;
-// tcgen05 ids: kPrefillBase + t (whole-K tiles, t < kPrefillWholeK), then
-// kPrefillBase + kPrefillWholeK + (t - kPrefillWholeK) * 4 + log2(cluster size) for the split-K tiles
-constexpr int kPrefillIds = kPrefillWholeK + (kPrefillTiles - kPrefillWholeK) * 4;
+// ids: kPrefillBase + t for the whole-K tiles t < 4; then 4 ids (cluster size 1, 2, 4, 8) for each of the two split-K
+// tiles; then the CTA-pair tile
+constexpr int kPrefillSplitTiles = 2;
+constexpr int kPrefillIds = kPrefillWholeK + kPrefillSplitTiles * 4 + 1;
 int prefill_id(int tile, int S) {
   if (tile < kPrefillWholeK) return kPrefillBase + tile;
+  if (tile == kPrefillPairTile) return kPrefillBase + kPrefillWholeK + kPrefillSplitTiles * 4;
   int l2 = 0;
   while ((1 << l2) < S) ++l2;
   return kPrefillBase + kPrefillWholeK + (tile - kPrefillWholeK) * 4 + l2;
@@ -308,6 +312,9 @@ void prefill_from_id(int id, int* tile, int* S) {
   const int r = id - kPrefillBase;
   if (r < kPrefillWholeK) {
     *tile = r;
+    *S = 1;
+  } else if (r == kPrefillWholeK + kPrefillSplitTiles * 4) {
+    *tile = kPrefillPairTile;
     *S = 1;
   } else {
     *tile = kPrefillWholeK + (r - kPrefillWholeK) / 4;

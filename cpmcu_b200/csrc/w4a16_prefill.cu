@@ -26,12 +26,14 @@ const TileShape kTiles[kPrefillTiles] = {
     // split-K over a thread-block cluster (mid M: the N x M grid alone cannot fill the machine)
     {1, 64, 0.f, "tc/bn128/bm64/splitk"},
     {1, 128, 0.f, "tc/bn128/bm128/splitk"},
+    // cta_group::2: a CTA pair per 256 columns x 256 tokens (whole K, persistent)
+    {1, 256, 0.f, "tc/pair256/bm256"},
 };
 
-template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT>
+template <typename T, int NSUB, int BM, int STAGES, int QSTAGES, int DW, bool GROUPED, bool SPLIT, bool PAIR = false>
 int launch_one(const GemmCall& g, int S, int* query) {
-  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
-  auto kern = w4a16_prefill_kernel<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT>;
+  using Cfg = PrefillCfg<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT, PAIR>;
+  auto kern = w4a16_prefill_kernel<T, NSUB, BM, STAGES, QSTAGES, DW, GROUPED, SPLIT, PAIR>;
   static bool attr_set = false;  // benign race: idempotent
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -89,7 +91,7 @@ int launch_one(const GemmCall& g, int S, int* query) {
   {  // activations: T [M][K], [BM x 64] boxes, 128B swizzle, rows past M zero-filled
     const uint64_t dims[2] = {static_cast<uint64_t>(g.k), static_cast<uint64_t>(g.m)};
     const uint64_t strides[1] = {static_cast<uint64_t>(g.k) * 2};
-    const uint32_t box[2] = {64, BM};
+    const uint32_t box[2] = {64, static_cast<uint32_t>(Cfg::A_ROWS)};
     if (int rc = get_tensor_map(&tm_a, g.a, Elem<T>::kTmaType, 2, dims, strides, box,
                                 CU_TENSOR_MAP_SWIZZLE_128B))
       return rc;
@@ -103,7 +105,7 @@ int launch_one(const GemmCall& g, int S, int* query) {
   args.m = g.m;
   args.n = g.n;
   args.k = g.k;
-  args.n_tiles = (g.n + Cfg::BN - 1) / Cfg::BN;
+  args.n_tiles = PAIR ? (g.n + 255) / 256 : (g.n + Cfg::BN - 1) / Cfg::BN;
   args.m_tiles = (g.m + BM - 1) / BM;
   args.kblks = g.k / 64;
   args.qkv_a = g.qkv_a;
@@ -115,6 +117,10 @@ int launch_one(const GemmCall& g, int S, int* query) {
     while (S & (S - 1)) --S;
     grid = static_cast<int>(tiles) * S;
   }
+  if (PAIR) {
+    const int pairs = sm_count() / 2;
+    grid = 2 * static_cast<int>(tiles < pairs ? tiles : pairs);
+  }
 
   cudaLaunchConfig_t cfg;
   std::memset(&cfg, 0, sizeof(cfg));
@@ -124,9 +130,9 @@ int launch_one(const GemmCall& g, int S, int* query) {
   cfg.stream = g.stream;
   cudaLaunchAttribute attr[2];
   int na = 0;
-  if (SPLIT && S > 1) {
+  if ((SPLIT && S > 1) || PAIR) {
     attr[na].id = cudaLaunchAttributeClusterDimension;
-    attr[na].val.clusterDim.x = S;
+    attr[na].val.clusterDim.x = PAIR ? 2 : S;
     attr[na].val.clusterDim.y = 1;
     attr[na].val.clusterDim.z = 1;
     ++na;
@@ -153,6 +159,7 @@ int launch_tile(const GemmCall& g, int tile, int S, int* query) {
     case 3: return launch_one<T, 1, 128, 6, 6, 8, GROUPED, false>(g, 1, query);
     case 4: return launch_one<T, 1, 64, 2, 10, 8, GROUPED, true>(g, S, query);
     case 5: return launch_one<T, 1, 128, 2, 8, 8, GROUPED, true>(g, S, query);
+    case 6: return launch_one<T, 1, 256, 5, 5, 8, GROUPED, false, true>(g, 1, query);
   }
   return fail(B200_W4A16_EINVAL, "tcgen05 tile id %d out of range", tile);
 }

@@ -578,3 +578,27 @@ def test_qkv_split_write(tdt, m):
     assert int(ws.abs().max()) == 0
     with pytest.raises(ValueError):
         b.gemm(a, qw, sc, ws, c_tmp, qkv_split=(qa, qb + 8))
+
+
+PAIR_CFG = 1013   # "tc/pair256/bm256": cta_group::2 CTA pairs
+
+
+@pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
+@pytest.mark.parametrize("m,k,n", [(256, 256, 256), (40, 256, 192), (300, 512, 448), (354, 1024, 640), (513, 512, 1152),
+                                   (1024, 1024, 2048)])
+def test_tcgen05_cta_pair_tile(dtype, m, k, n):
+    """cta_group::2: a CTA pair per 256 weight columns x 256 tokens (each CTA dequantises 128 columns and stages half of
+    the token tile).  Oracle-correct on ragged token tiles (the pair splits the VALID tokens) and on N that is not a
+    multiple of 256 (the second CTA's columns are zero-filled / masked), bit-identical run to run and bit-identical
+    to the single-CTA tiles (same k order)."""
+    from cpmcu_b200 import capi as L
+    assert L.config_name(PAIR_CFG) == "tc/pair256/bm256"
+    prob = mo.make_problem(m, k, n, 128, dtype, seed=m + n)
+    c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, dtype)
+    out1, _ = run_ours(prob, m, n, k, dtype, force_config=PAIR_CFG)
+    out2, _ = run_ours(prob, m, n, k, dtype, force_config=PAIR_CFG, pdl=True)
+    assert torch.equal(out1, out2)
+    st = mo.error_stats(t_load(out1, dtype), exact, dtype)
+    assert st["max_rel"] <= TOL_MAX_REL, st
+    single, _ = run_ours(prob, m, n, k, dtype, force_config=1002)
+    assert torch.equal(out1, single)
