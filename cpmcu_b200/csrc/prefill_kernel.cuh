@@ -67,7 +67,7 @@ struct PrefillCfg {
   static constexpr int OFF_Q = OFF_W + STAGES * W_STAGE;
   static constexpr int OFF_S = OFF_Q + QSTAGES * Q_STAGE;
   static constexpr int OFF_BAR = (OFF_S + QSTAGES * S_STAGE + 127) / 128 * 128;
-  static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4;
+  static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4 + (PAIR ? STAGES : 0);
   static constexpr int SMEM_BYTES = OFF_BAR + NBARS * 8 + 16;
   static constexpr int THREADS = (7 + DW) * 32;
   static_assert(DWG % CHUNKS == 0 && WPC >= 1 && 4 % WPC == 0, "dequant warp layout");
@@ -101,17 +101,21 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
   const uint32_t bar_q_empty = bar_q_full + QSTAGES * 8;
   const uint32_t bar_acc_full = bar_q_empty + QSTAGES * 8;
   const uint32_t bar_acc_empty = bar_acc_full + 2 * 8;
+  const uint32_t bar_w_peer = bar_acc_empty + 2 * 8;   // PAIR, leader's copy: the peer CTA's half of the W operand is written
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + Cfg::OFF_BAR + Cfg::NBARS * 8);
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle: provably warp-uniform for ptxas, so the role branches are uniform branches and the
+  // single-lane roles (UMMA issuer, TMA producers) keep their loop state and descriptors in uniform registers
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(bar_a_full + 8 * s, 1);
-      mbar_init(bar_w_full + 8 * s, PAIR ? 2 * Cfg::DWG : Cfg::DWG);   // PAIR: the peer's dequantisers arrive here too
+      mbar_init(bar_w_full + 8 * s, Cfg::DWG);
       mbar_init(bar_consumed + 8 * s, 1);
+      if (PAIR) mbar_init(bar_w_peer + 8 * s, 1);
     }
 #pragma unroll
     for (int s = 0; s < QSTAGES; ++s) {
@@ -160,7 +164,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 
   if (warp == 4) {
     // ============================== TMA producer: activations (ring A) ==============================
-    if (lane == 0) {
+    if (elect_one()) {
       tma_prefetch_desc(&tm_a);
       pdl_wait_prior_grids();
       int it = 0;
@@ -190,7 +194,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
     // ===================== TMA producer: raw int4 weights + group scales (ring Q) =====================
     // its own lane and its own, deeper ring: the HBM stream runs QSTAGES boxes ahead of the dequantisers
     // independently of the activation / tensor-core pipeline
-    if (lane == 0) {
+    if (elect_one()) {
       tma_prefetch_desc(&tm_w);
       if (GROUPED) tma_prefetch_desc(&tm_s);
       int it = 0;
@@ -211,8 +215,17 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
     }
   } else if (warp == 5 && prank == 0) {
     // ======================================= MMA issuer =======================================
-    // (PAIR: the leader CTA only; one instruction drives both SMs' tensor cores)
-    int it = 0, acc_it = 0;
+    // (PAIR: the leader CTA only; one instruction drives both SMs' tensor cores.)  The warp stays convergent; one
+    // elected lane issues.  Everything the UMMAs take is warp-uniform by construction (ring slot, descriptors = base +
+    // slot * stride, TMEM address through a shuffle), so a k-block is 2 waits + 4 UTCHMMA + 1 commit and a few uniform
+    // adds — the round-2 profile (profiles/r02/i_*) had this loop at ~140 instructions per k-block with a
+    // register -> uniform-register waterfall before every UMMA, which capped the tensor pipe at 54 %.
+    const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
+    constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO = 8 rows x 128 B | version | SWIZZLE_128B
+    const uint32_t a_lo0 = (((sbase + Cfg::OFF_A) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t w_lo0 = (((sbase + Cfg::OFF_W) & 0x3FFFFu) >> 4) | (1u << 16);
+    uint32_t s = 0, ph = 0;
+    int acc_it = 0;
     for (int tile = tile_begin; tile < total_tiles; tile += tile_step, ++acc_it) {
       const int mt = tile % p.m_tiles;
       const int acc = acc_it % Cfg::ACC_STAGES;
@@ -221,24 +234,24 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       int vt = p.m - mt * BM;
       vt = vt > BM ? BM : vt;
       const uint32_t idesc = umma_idesc_f16<T>(PAIR ? 256 : 128, static_cast<uint32_t>((vt + 15) & ~15));
-      const uint32_t d0 = tmem_base + acc * Cfg::ACC_COLS;
-      for (int kb = kb_lo; kb < kb_hi; ++kb, ++it) {
-        const int s = it % STAGES;
-        const uint32_t ph = (it / STAGES) & 1;
+      const uint32_t d0 = tm + acc * Cfg::ACC_COLS;
+      for (int kb = kb_lo; kb < kb_hi; ++kb) {
         mbar_wait(bar_a_full + 8 * s, ph);
         mbar_wait(bar_w_full + 8 * s, ph);
+        if (PAIR) mbar_wait_cluster(bar_w_peer + 8 * s, ph);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_addr = sbase + Cfg::OFF_A + s * Cfg::A_STAGE;
-          const uint32_t w_addr = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
+        if (elect_one()) {
+          const uint32_t a_lo = a_lo0 + s * (Cfg::A_STAGE >> 4);
+          const uint32_t w_lo = w_lo0 + s * (Cfg::W_STAGE >> 4);
 #pragma unroll
           for (int sub = 0; sub < NSUB; ++sub) {
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
-              const uint64_t adesc = umma_desc_k_sw128(w_addr + sub * 16384 + kk * 32);
-              const uint64_t bdesc = umma_desc_k_sw128(a_addr + kk * 32);
-              if (PAIR) tc_mma_f16_pair(d0 + sub * BM, adesc, bdesc, idesc, (kb != kb_lo || kk != 0) ? 1u : 0u);
-              else tc_mma_f16(d0 + sub * BM, adesc, bdesc, idesc, (kb != kb_lo || kk != 0) ? 1u : 0u);
+              const uint64_t adesc = (static_cast<uint64_t>(kDescHi) << 32) | (w_lo + sub * 1024 + kk * 2);
+              const uint64_t bdesc = (static_cast<uint64_t>(kDescHi) << 32) | (a_lo + kk * 2);
+              const uint32_t accum = (kk != 0 || kb != kb_lo) ? 1u : 0u;
+              if (PAIR) tc_mma_f16_pair(d0 + sub * BM, adesc, bdesc, idesc, accum);
+              else tc_mma_f16(d0 + sub * BM, adesc, bdesc, idesc, accum);
             }
           }
           if (PAIR) {   // frees the A / W slots and publishes the accumulator in BOTH CTAs
@@ -250,6 +263,28 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
           }
         }
         __syncwarp();
+        if (++s == STAGES) {
+          s = 0;
+          ph ^= 1u;
+        }
+      }
+    }
+  } else if (PAIR && warp == 5) {
+    // ============ PAIR, peer CTA: forwards "my half of W stage s is written" to the leader ============
+    // The dequantisers arrive on their OWN CTA's w_full (a cheap CTA-scope release); this otherwise idle warp turns a
+    // completed phase into ONE cluster-scope arrive on the leader's w_peer.  (Eight dequant warps each doing the
+    // remote release themselves spent half their time in the cluster-scope fence: profiles/r02/i_*.)
+    int my_tiles = 0;
+    for (int tile = tile_begin; tile < total_tiles; tile += tile_step) ++my_tiles;
+    const int total_its = my_tiles * (kb_hi - kb_lo);
+    uint32_t s = 0, ph = 0;
+    for (int it = 0; it < total_its; ++it) {
+      mbar_wait(bar_w_full + 8 * s, ph);
+      if (elect_one()) mbar_arrive_leader(bar_w_peer + 8 * s);
+      __syncwarp();
+      if (++s == STAGES) {
+        s = 0;
+        ph ^= 1u;
       }
     }
   } else if (warp >= 7) {
@@ -306,10 +341,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       // shared-memory loads are then complete by data dependence, not by an assumption about issue order
       // (releasing right after ISSUING the loads was the round-1 split-K race)
       if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);
-      if (lane == 0) {
-        if (PAIR) mbar_arrive_leader(bar_w_full + 8 * s);   // the leader's issuer waits for both CTAs' halves of the W operand
-        else mbar_arrive(bar_w_full + 8 * s);
-      }
+      if (lane == 0) mbar_arrive(bar_w_full + 8 * s);   // PAIR: the peer CTA's warp 5 forwards the completed phase
       sq += Cfg::DGROUPS;
       if (sq >= QSTAGES) { sq -= QSTAGES; qph ^= 1u; }
       s += Cfg::DGROUPS;

@@ -14,7 +14,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--k", type=int, default=4096)
 ap.add_argument("--n", type=int, default=32768)
 ap.add_argument("--m", type=int, default=1)
-ap.add_argument("--cfg", type=int, default=0)
+ap.add_argument("--cfg", default="0", help="configuration id, or several separated by commas (each launched in turn)")
 ap.add_argument("--copies", type=int, default=6)
 ap.add_argument("--pdl", action="store_true")
 ap.add_argument("--cfg-name", default="", help="pick the configuration id by (sub)name, e.g. __half/nt1/tn4x64/kb8x16/w8")
@@ -22,7 +22,7 @@ a_ = ap.parse_args()
 dev = "cuda"
 if a_.cfg_name:
     from cpmcu_b200 import capi as _L
-    a_.cfg = next(c for c in list(range(1, 400)) if a_.cfg_name in (_L.config_name(c) or ""))
+    a_.cfg = "%d" % next(c for c in list(range(1, 400)) if a_.cfg_name in (_L.config_name(c) or ""))
     print("cfg", a_.cfg, _L.config_name(a_.cfg))
 k, n, m = a_.k, a_.n, a_.m
 qw = torch.randint(-2**31, 2**31 - 1, (a_.copies, k // 16, 2 * n), dtype=torch.int32, device=dev)
@@ -31,8 +31,9 @@ a = torch.randn((m, k), device=dev).half()
 out = torch.empty((m, n), dtype=torch.float16, device=dev)
 ws = torch.zeros(B.workspace_ints(n), dtype=torch.int32, device=dev)
 ct = torch.empty(max(B.reduce_bytes_fast(m, n, k) // 4, 64), dtype=torch.float32, device=dev)
-for rep in range(2):
-    for i in range(a_.copies):
-        B.gemm(a, qw[i], sc[i], ws, ct, out=out, force_config=a_.cfg, pdl=a_.pdl)
+for cfg in [int(c) for c in str(a_.cfg).split(",")]:
+    for rep in range(2):
+        for i in range(a_.copies):
+            B.gemm(a, qw[i], sc[i], ws, ct, out=out, force_config=cfg, pdl=a_.pdl)
 torch.cuda.synchronize()
 print("done", B.launch_count())

@@ -2,7 +2,7 @@
 """One small launch per kernel family, for compute-sanitizer (racecheck / synccheck / memcheck):
   compute-sanitizer --tool racecheck python tools/sanitize_case.py
 Families: streaming kernel with split columns (M = 4, 20, 32), whole-column plan (contract-sized scratch), gated SiLU,
-tcgen05 split-K (M = 64) and whole-K (M = 300), the un-quantised streaming linear, dequant dump, repack."""
+tcgen05 split-K (M = 64), whole-K (M = 300) and the CTA-pair tile, the un-quantised streaming linear, dequant dump, repack."""
 import os
 import sys
 
@@ -39,6 +39,7 @@ case(16, 1024, 512, contract=True)
 case(8, 512, 1024, gated_silu=True)
 case(64, 1024, 256)
 case(300, 512, 384)
+case(300, 512, 512, force_config=1013)   # cta_group::2 pair tile
 w = torch.randn((1024, 512), device=dev, generator=g).half()
 x = torch.randn((4, 512), device=dev, generator=g).half()
 B.dense_linear(x, w)
