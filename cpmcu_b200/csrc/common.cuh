@@ -47,20 +47,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       : "memory");
 }
 
-// wait with cluster-scope acquire: the arrival comes from the peer CTA of a pair
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred P1;\n"
-      "LAB_WAIT:\n"
-      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n"
-      "@P1 bra DONE;\n"
-      "bra LAB_WAIT;\n"
-      "DONE:\n"
-      "}\n" ::"r"(bar),
-      "r"(parity)
-      : "memory");
-}
 // same, for waits that are expected to be long (a whole main loop): back off between polls so the
 // spinning warp does not take issue slots from the warps doing the work
 __device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity, uint32_t ns) {
@@ -263,10 +249,13 @@ __device__ __forceinline__ void tc_mma_f16_pair(uint32_t tmem_d, uint64_t adesc,
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-// arrive on the barrier at `bar`'s offset in cluster rank 0 (release at cluster scope: the arriving warp's shared-memory
-// writes — made visible to the async proxy by its own fence.proxy.async — are ordered before the leader's wait)
+// arrive on the barrier at `bar`'s offset in cluster rank 0.  Plain remote arrive (the form CUTLASS's
+// ClusterBarrier::arrive(cta_id) emits): what it publishes is the arriving warp's OWN-CTA shared memory, already made
+// visible to that SM's async proxy by the warp's fence.proxy.async, and read only by that SM's tensor core after the
+// leader's wait.  The `.release.cluster` form puts a cluster-scope fence (ERRBAR, ~1 us) in front of every arrive: with
+// it the eight dequant warps spent half their time fencing (profiles/r02/i_*).
 __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
 }
 // TMA load whose transaction bytes are credited to the LEADER's barrier (executed by both CTAs of the pair)
 __device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
@@ -363,6 +352,25 @@ __device__ __forceinline__ size_t out_offset(int tok, int n, int n_total, int m_
   if (n < qa) return static_cast<size_t>(tok) * qa + n;
   if (n < qa + qb) return static_cast<size_t>(m_total) * qa + static_cast<size_t>(tok) * qb + (n - qa);
   return static_cast<size_t>(m_total) * (qa + qb) + static_cast<size_t>(tok) * qb + (n - qa - qb);
+}
+
+// The same mapping seen from one output column: offset of (token 0, column n) and the token stride, so that
+// out_offset(tok, n, ...) == *col_off + tok * *tok_stride.  An epilogue whose thread owns a column hoists this.
+__device__ __forceinline__ void out_column(int n, int n_total, int m_total, int qa, int qb, size_t* col_off,
+                                           int* tok_stride) {
+  if (qa == 0) {
+    *col_off = static_cast<size_t>(n);
+    *tok_stride = n_total;
+  } else if (n < qa) {
+    *col_off = static_cast<size_t>(n);
+    *tok_stride = qa;
+  } else if (n < qa + qb) {
+    *col_off = static_cast<size_t>(m_total) * qa + (n - qa);
+    *tok_stride = qb;
+  } else {
+    *col_off = static_cast<size_t>(m_total) * (qa + qb) + (n - qa - qb);
+    *tok_stride = qb;
+  }
 }
 
 // D(16x8,f32) += A(16x16,T,row) * B(16x8,T,col): the register-operand tensor path.  In the

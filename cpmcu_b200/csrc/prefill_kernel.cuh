@@ -67,7 +67,7 @@ struct PrefillCfg {
   static constexpr int OFF_Q = OFF_W + STAGES * W_STAGE;
   static constexpr int OFF_S = OFF_Q + QSTAGES * Q_STAGE;
   static constexpr int OFF_BAR = (OFF_S + QSTAGES * S_STAGE + 127) / 128 * 128;
-  static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4 + (PAIR ? STAGES : 0);
+  static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4;
   static constexpr int SMEM_BYTES = OFF_BAR + NBARS * 8 + 16;
   static constexpr int THREADS = (7 + DW) * 32;
   static_assert(DWG % CHUNKS == 0 && WPC >= 1 && 4 % WPC == 0, "dequant warp layout");
@@ -101,7 +101,6 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
   const uint32_t bar_q_empty = bar_q_full + QSTAGES * 8;
   const uint32_t bar_acc_full = bar_q_empty + QSTAGES * 8;
   const uint32_t bar_acc_empty = bar_acc_full + 2 * 8;
-  const uint32_t bar_w_peer = bar_acc_empty + 2 * 8;   // PAIR, leader's copy: the peer CTA's half of the W operand is written
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + Cfg::OFF_BAR + Cfg::NBARS * 8);
 
   // warp index through a shuffle: provably warp-uniform for ptxas, so the role branches are uniform branches and the
@@ -113,9 +112,8 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(bar_a_full + 8 * s, 1);
-      mbar_init(bar_w_full + 8 * s, Cfg::DWG);
+      mbar_init(bar_w_full + 8 * s, PAIR ? 2 * Cfg::DWG : Cfg::DWG);   // PAIR: the peer's dequantisers arrive here too
       mbar_init(bar_consumed + 8 * s, 1);
-      if (PAIR) mbar_init(bar_w_peer + 8 * s, 1);
     }
 #pragma unroll
     for (int s = 0; s < QSTAGES; ++s) {
@@ -238,7 +236,6 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       for (int kb = kb_lo; kb < kb_hi; ++kb) {
         mbar_wait(bar_a_full + 8 * s, ph);
         mbar_wait(bar_w_full + 8 * s, ph);
-        if (PAIR) mbar_wait_cluster(bar_w_peer + 8 * s, ph);
         tc_fence_after();
         if (elect_one()) {
           const uint32_t a_lo = a_lo0 + s * (Cfg::A_STAGE >> 4);
@@ -267,24 +264,6 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
           s = 0;
           ph ^= 1u;
         }
-      }
-    }
-  } else if (PAIR && warp == 5) {
-    // ============ PAIR, peer CTA: forwards "my half of W stage s is written" to the leader ============
-    // The dequantisers arrive on their OWN CTA's w_full (a cheap CTA-scope release); this otherwise idle warp turns a
-    // completed phase into ONE cluster-scope arrive on the leader's w_peer.  (Eight dequant warps each doing the
-    // remote release themselves spent half their time in the cluster-scope fence: profiles/r02/i_*.)
-    int my_tiles = 0;
-    for (int tile = tile_begin; tile < total_tiles; tile += tile_step) ++my_tiles;
-    const int total_its = my_tiles * (kb_hi - kb_lo);
-    uint32_t s = 0, ph = 0;
-    for (int it = 0; it < total_its; ++it) {
-      mbar_wait(bar_w_full + 8 * s, ph);
-      if (elect_one()) mbar_arrive_leader(bar_w_peer + 8 * s);
-      __syncwarp();
-      if (++s == STAGES) {
-        s = 0;
-        ph ^= 1u;
       }
     }
   } else if (warp >= 7) {
@@ -341,7 +320,10 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       // shared-memory loads are then complete by data dependence, not by an assumption about issue order
       // (releasing right after ISSUING the loads was the round-1 split-K race)
       if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);
-      if (lane == 0) mbar_arrive(bar_w_full + 8 * s);   // PAIR: the peer CTA's warp 5 forwards the completed phase
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_leader(bar_w_full + 8 * s);   // the leader's issuer waits for both CTAs' halves of the W operand
+        else mbar_arrive(bar_w_full + 8 * s);
+      }
       sq += Cfg::DGROUPS;
       if (sq >= QSTAGES) { sq -= QSTAGES; qph ^= 1u; }
       s += Cfg::DGROUPS;
@@ -369,6 +351,16 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
         T bias_v = Elem<T>::from_float(0.f), chan_s = Elem<T>::from_float(1.f);
         if (nok && p.bias) bias_v = reinterpret_cast<const T*>(p.bias)[n];
         if (!GROUPED && nok) chan_s = reinterpret_cast<const T*>(p.scales)[chan_scale_pos(n)];
+        // this thread owns output column n for the whole tile: its base offset and token stride are tile constants
+        // (q/k/v split included), and the post-op set is a kernel constant — the per-element work of the common case
+        // is one conversion and one store (the round-2 profile had ~30 branchy instructions per element here, and the
+        // issuer waiting for the accumulator 29 % of the time at K = 4096: profiles/r02/i_*)
+        size_t col_off = 0;
+        int tok_stride = 0;
+        out_column(nok ? n : 0, p.n, p.m, p.qkv_a, p.qkv_b, &col_off, &tok_stride);
+        T* cptr = cbase + col_off + static_cast<size_t>(m0) * tok_stride;
+        const T* rptr = rbase ? rbase + col_off + static_cast<size_t>(m0) * tok_stride : nullptr;
+        const bool plain = GROUPED && !rbase && !p.bias && p.out_scale == 0u;
 #pragma unroll 1
         for (int c0 = 0; c0 < vt; c0 += 32) {
           uint32_t v[32];
@@ -383,17 +375,23 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
             for (int i = 0; i < 32; ++i)
               red[(c0 + i) * Cfg::RED_PITCH + qd * 32 + lane] = __uint_as_float(v[i]);
           } else if (nok) {
+            T* cp = cptr + static_cast<size_t>(c0) * tok_stride;
+            if (plain && c0 + 32 <= vt) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              const int tok = m0 + c0 + i;
-              if (tok < p.m) {
-                T o = Elem<T>::from_float(__uint_as_float(v[i]));
-                if (!GROUPED) o = __hmul(o, chan_s);  // channelwise: scale the ROUNDED sum
-                const size_t off = out_offset(tok, n, p.n, p.m, p.qkv_a, p.qkv_b);
-                if (rbase) o = __hadd(rbase[off], o);
-                if (p.bias) o = __hadd(o, bias_v);
-                o = apply_out_scale<T>(o, p.out_scale);
-                cbase[off] = o;
+              for (int i = 0; i < 32; ++i) cp[static_cast<size_t>(i) * tok_stride] = Elem<T>::from_float(__uint_as_float(v[i]));
+            } else {
+              const T* rp = rptr ? rptr + static_cast<size_t>(c0) * tok_stride : nullptr;
+              const int cnt = vt - c0;
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                if (i < cnt) {
+                  T o = Elem<T>::from_float(__uint_as_float(v[i]));
+                  if (!GROUPED) o = __hmul(o, chan_s);  // channelwise: scale the ROUNDED sum
+                  if (rp) o = __hadd(rp[static_cast<size_t>(i) * tok_stride], o);
+                  if (p.bias) o = __hadd(o, bias_v);
+                  o = apply_out_scale<T>(o, p.out_scale);
+                  cp[static_cast<size_t>(i) * tok_stride] = o;
+                }
               }
             }
           }

@@ -10,5 +10,5 @@ done
 python tools/chain.py --m 64 --layers 4 --reps 5 --combo ""
 python tools/chain.py --m 128 --layers 4 --reps 5 --combo ""
 python tools/chain.py --m 256 --layers 4 --reps 5 --combo ""
-} > gpurun_out/chain17.txt 2>&1
-awk '{ printf "%s %s us %s GB/s  %s\n", $1,$2,$4,$6 }' gpurun_out/chain17.txt | cut -c1-120
+} > gpurun_out/chain20.txt 2>&1
+awk '{ printf "%s %s us %s GB/s  %s\n", $1,$2,$4,$6 }' gpurun_out/chain20.txt | cut -c1-120
