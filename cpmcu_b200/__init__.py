@@ -20,6 +20,7 @@ from .capi import (  # noqa: F401
     reduce_bytes,
     reduce_bytes_fast,
     set_scratch_capacity,
+    gemm_static_scratch,
     reduce_max_m,
     workspace_ints,
     launch_count,

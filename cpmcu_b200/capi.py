@@ -79,6 +79,8 @@ SYMBOLS = {
     "b200_w4a16_reduce_bytes": (c_int64, [c_int64, c_int64, c_int64]),
     "b200_w4a16_reduce_bytes_fast": (c_int64, [c_int64, c_int64, c_int64]),
     "b200_w4a16_set_scratch_capacity": (c_int64, [c_int64]),
+    "b200_w4a16_gemm_static_scratch": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int,
+                                               c_int, c_void_p]),
     "b200_w4a16_workspace_ints": (c_int64, [c_int64]),
     "b200_w4a16_launch_count": (c_int64, []),
     "b200_w4a16_set_pdl": (c_int, [c_int]),
@@ -207,6 +209,19 @@ def gemm(a, qweight, scales, workspace, c_tmp, out=None, *, group_size=128, perm
                                   _ptr(out), m, n, k, group_size, dtype_code(a.dtype), 1,
                                   0 if perm is None else 1, _ptr(a_tmp), _ptr(c_tmp), _stream(stream),
                                   ctypes.byref(o))
+    if rc:
+        _raise(rc)
+    return out
+
+
+def gemm_static_scratch(a, qweight, scales, out, *, group_size=128, stream=None):
+    """The M <= 32 GEMM through b200_w4a16_gemm_static_scratch: no workspace / c_tmp arguments, the library's file-scope
+    device array serves as scratch and the call allocates nothing (so `out` is required).  No counterpart in the
+    reference.  Calls on one device share the array: keep them on one stream."""
+    m, k = a.shape
+    n = qweight.shape[1] // 2
+    rc = lib().b200_w4a16_gemm_static_scratch(_ptr(a), _ptr(qweight), _ptr(scales), _ptr(out), m, n, k, group_size,
+                                              dtype_code(a.dtype), _stream(stream))
     if rc:
         _raise(rc)
     return out

@@ -722,4 +722,67 @@ int b200_w4a16_allreduce_oneshot(const void* const* peer_in, int32_t* const* pee
   return b200_w4a16_allreduce(peer_in, nullptr, peer_sig, epoch, out, elems, dtype, rank, world, 0, stream);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// b200_w4a16_gemm_static_scratch: the streaming GEMM with its scratch in a file-scope device array — for callers that
+// may not allocate (include/b200_w4a16.h).  No counterpart in the reference.
+// Layout of the array: [partial tiles: B200_W4A16_STATIC_SCRATCH_BYTES][ticket counters: ..._COUNTER_BYTES].
+// In HOST code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address handed to the
+// kernel comes from cudaGetSymbolAddress, resolved once per device with that device current.
+static __device__ __align__(256) unsigned char
+    g_static_scratch[B200_W4A16_STATIC_SCRATCH_BYTES + B200_W4A16_STATIC_COUNTER_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[kMaxDevices] = {};
+
+// device address of the array on the CURRENT device (set-up: once per device); null + error string on failure
+unsigned char* static_scratch_ptr() {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    b200::fail(B200_W4A16_ECUDA, "gemm_static_scratch: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (e != cudaSuccess || !ptr) {
+      b200::fail(B200_W4A16_ECUDA, "gemm_static_scratch: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+      return nullptr;
+    }
+    g_static_ptr[dev] = static_cast<unsigned char*>(ptr);
+  }
+  return g_static_ptr[dev];
+}
+}  // namespace
+
+int b200_w4a16_gemm_static_scratch(const void* a, const int32_t* qweight, const void* scales, void* c, int64_t m,
+                                   int64_t n, int64_t k, int group_size, int dtype, void* stream) {
+  using namespace b200;
+  if (m > B200_W4A16_STATIC_MAX_M)
+    return fail(B200_W4A16_EINVAL, "gemm_static_scratch: M = %lld exceeds the maximum of %d (the static scratch serves the "
+                "streaming kernel only; use b200_w4a16_gemm for wider inputs)", (long long)m, B200_W4A16_STATIC_MAX_M);
+  if (n > B200_W4A16_STATIC_MAX_N)
+    return fail(B200_W4A16_EINVAL, "gemm_static_scratch: N = %lld exceeds the maximum of %d (ticket counters of the static "
+                "array)", (long long)n, B200_W4A16_STATIC_MAX_N);
+  if (n > 0 && b200_w4a16_workspace_ints(n) * 4 > B200_W4A16_STATIC_COUNTER_BYTES)
+    return fail(B200_W4A16_EINVAL, "gemm_static_scratch: N = %lld needs more ticket counters than the static array holds", (long long)n);
+  unsigned char* base = static_scratch_ptr();
+  if (!base) return B200_W4A16_ECUDA;
+  float* c_tmp = reinterpret_cast<float*>(base);
+  int32_t* counters = reinterpret_cast<int32_t*>(base + B200_W4A16_STATIC_SCRATCH_BYTES);
+  // the array keeps the previous call's contents; the partial tiles are written before they are read, the counters must
+  // start at zero (the kernel leaves them at zero, but a launch that faulted may not have)
+  cudaError_t e = cudaMemsetAsync(counters, 0, B200_W4A16_STATIC_COUNTER_BYTES, reinterpret_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail(B200_W4A16_ECUDA, "gemm_static_scratch: cudaMemsetAsync: %s", cudaGetErrorString(e));
+  b200_w4a16_opts o;
+  std::memset(&o, 0, sizeof(o));
+  o.c_tmp_bytes = B200_W4A16_STATIC_SCRATCH_BYTES;   // plan_decode stays inside it
+  o.pdl = 0;                                          // calls share the array: never overlap the previous launch
+  return gemm_impl(a, qweight, scales, nullptr, nullptr, counters, c, m, n, k, group_size, dtype, 1, 0, nullptr, c_tmp,
+                   stream, &o, nullptr);
+}
+
 }  // extern "C"

@@ -198,6 +198,29 @@ int b200_w4a16_gemm_ar(const void* a, const int32_t* qweight, const void* scales
                        int64_t m, int64_t n, int64_t k, int group_size, int dtype, float* c_tmp, void* stream,
                        const b200_w4a16_opts* opts, const b200_w4a16_ar* ar);
 
+/* The decode-regime GEMM (M <= 32, the streaming kernel) for callers that cannot allocate device memory (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * Same arithmetic as b200_w4a16_gemm; the caller passes only inputs and the
+ * output — the split-column scratch (fp32 partial tiles) and the per-column-tile ticket counters live in ONE
+ * file-scope `static __device__` array inside the library:
+ *   B200_W4A16_STATIC_SCRATCH_BYTES (4 MiB) of partial tiles + B200_W4A16_STATIC_COUNTER_BYTES (64 KiB) of counters,
+ *   held by every GPU that loads the library until the process exits.
+ * Limits (B200_W4A16_EINVAL with a message beyond them): M <= 32, N <= B200_W4A16_STATIC_MAX_N (65536), fp16 / bf16,
+ * group_size 128 or -1, no act-order.  Inside the limits every shape runs: where full-width stream-K would need more
+ * than 4 MiB the launch plan splits fewer columns (plan_decode), results stay within the parity tolerance.
+ * The call makes no cudaMalloc / cudaFree / allocating library call: the array's device address is resolved once per
+ * device (cudaGetSymbolAddress, with that device current) and the counters are cleared with cudaMemsetAsync on
+ * `stream` before every launch (a launch that faulted may have left a ticket behind).
+ * EVERY call on a device shares the array and it keeps the previous call's contents: calls that overlap on the GPU
+ * (two streams, or PDL-chained launches of this entry point) RACE on it — serialise them (one stream, which this
+ * entry point enforces for itself by launching without the PDL attribute). */
+#define B200_W4A16_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+#define B200_W4A16_STATIC_COUNTER_BYTES (64 * 1024)
+#define B200_W4A16_STATIC_MAX_M 32
+#define B200_W4A16_STATIC_MAX_N 65536
+int b200_w4a16_gemm_static_scratch(const void* a, const int32_t* qweight, const void* scales, void* c, int64_t m,
+                                   int64_t n, int64_t k, int group_size, int dtype, void* stream);
+
 /* Process-wide default for programmatic dependent launch on entry points that take no opts
  * (b200_w4a16_gemm, b200_w4a16_linear_forward): 1 = every GEMM launch carries the PDL attribute so
  * its weight prefetch overlaps the tail of the previous kernel in the stream (safe with any
