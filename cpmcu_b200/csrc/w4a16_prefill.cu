@@ -205,6 +205,16 @@ void prefill_pick(const GemmCall& g, int* tile_out, int* S_out) {
       return;
     }
   }
+  // CTA pairs (256 columns x 256 tokens per pair, half the activation traffic per SM) once there is about a wave of
+  // pair tiles for the 74 pairs: measured per shape and M in profiles/r02/j_pair_vs_single_sweep.txt
+  {
+    const long long pair_tiles = static_cast<long long>((n + 255) / 256) * ((m + 255) / 256);
+    if (m > 256 && pair_tiles >= 64) {
+      *tile_out = kPrefillPairTile;
+      *S_out = 1;
+      return;
+    }
+  }
   int best = 0;
   float best_score = -1.f;
   for (int t = 0; t < 4; ++t) {

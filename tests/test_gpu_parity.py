@@ -602,3 +602,36 @@ def test_tcgen05_cta_pair_tile(dtype, m, k, n):
     assert st["max_rel"] <= TOL_MAX_REL, st
     single, _ = run_ours(prob, m, n, k, dtype, force_config=1002)
     assert torch.equal(out1, single)
+
+
+@pytest.mark.parametrize("m", [1024, 354])
+def test_tcgen05_pair_tile_repeatable_under_pdl_chains(m):
+    """the chunked-prefill chain as the operator runs it (auto-picked tiles: CTA pairs where a wave of pair tiles exists,
+    single-CTA tiles elsewhere; PDL on, so every kernel's weight stream and dequantisers start under the previous
+    kernel's tail and cluster launches interleave with non-cluster ones): 40 passes over 2 layers x {qkv, o, gate_up,
+    down} at the MiniCPM4-8B sizes, every output bit-identical to the single-CTA tile's on every pass."""
+    b = _b()
+    from cpmcu_b200 import capi as L
+    shapes = [(4096, 4608), (4096, 4096), (4096, 32768), (16384, 4096)]
+    picked = [L.config_name(L.pick_config(m, n, k, 128, L.FP16)) for k, n in shapes]
+    assert any("pair256" in p for p in picked), picked
+    g = torch.Generator(device=DEV).manual_seed(77)
+    layers = 2
+    w = []
+    for k, n in shapes:
+        for _ in range(layers):
+            qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=DEV, generator=g)
+            sc = (torch.rand((k // 128, n), device=DEV, generator=g) * 0.018 + 0.002).half()
+            a = torch.randn((m, k), device=DEV, generator=g).half()
+            w.append((a, qw, sc, torch.zeros(b.workspace_ints(n), dtype=torch.int32, device=DEV)))
+    c_tmp = torch.empty(b.reduce_max_m(m) * 32768, dtype=torch.float32, device=DEV)
+    refs = [b.gemm(a, qw, sc, ws, c_tmp, force_config=1002) for a, qw, sc, ws in w]
+    outs = [torch.empty_like(r) for r in refs]
+    torch.cuda.synchronize()
+    for rep in range(40):
+        for (a, qw, sc, ws), o in zip(w, outs):
+            b.gemm(a, qw, sc, ws, c_tmp, out=o, pdl=True)
+        torch.cuda.synchronize()
+        for i, (o, r) in enumerate(zip(outs, refs)):
+            assert torch.equal(o, r), f"pass {rep}, GEMM {i} ({picked[i // layers]}): differs from the single-CTA tile"
+            o.fill_(float("nan"))
