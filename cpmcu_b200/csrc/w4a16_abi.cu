@@ -291,8 +291,9 @@ const char* decode_name(int id) {
   int dtype, nt, geom;
   bool grouped;
   decode_from_id(id, &dtype, &nt, &grouped, &geom);
-  snprintf(buf, sizeof(buf), "%s/nt%d/tn%dx64/kb%dx16/w%d/s%d/%s", dtype == 0 ? "__half" : "__nv_bfloat16", nt,
-           kGeom[geom].chunks, kGeom[geom].krows, kGeom[geom].warps, kGeom[geom].stages, grouped ? "true" : "false");
+  snprintf(buf, sizeof(buf), "%s/nt%d/tn%dx64/kb%dx16/w%d/s%d/%s%s", dtype == 0 ? "__half" : "__nv_bfloat16", nt,
+           kGeom[geom].chunks, kGeom[geom].krows, kGeom[geom].warps, kGeom[geom].stages, grouped ? "true" : "false",
+           geom == kTcGeom ? "/tmem" : "");
   return buf;
 }
 

@@ -194,7 +194,7 @@ def test_all_decode_configs_agree():
         name = L.config_name(cfg)
         if not name:
             break
-        if not name.startswith("__half/nt2/") or not name.endswith("true"):
+        if not name.startswith("__half/nt2/") or not (name.endswith("true") or name.endswith("true/tmem")):
             continue
         out1, _ = run_ours(prob, m, n, k, mo.FP16, force_config=cfg)
         out2, _ = run_ours(prob, m, n, k, mo.FP16, force_config=cfg, pdl=True)
@@ -206,6 +206,67 @@ def test_all_decode_configs_agree():
         assert st["max_rel"] <= TOL_MAX_REL and st3["max_rel"] <= TOL_MAX_REL, (name, st, st3)
         seen += 1
     assert seen >= 5
+
+
+def tmem_config(dtype, m, group):
+    """force_config id of the tensor-memory streaming kernel (geometry 7, '/tmem') for this dtype / width / scale kind"""
+    from cpmcu_b200 import capi as L
+    nt = 1 if m <= 8 else (2 if m <= 16 else 4)
+    want = f"{'__half' if dtype == mo.FP16 else '__nv_bfloat16'}/nt{nt}/tn4x64/kb8x16/w8/s5/{'true' if group != -1 else 'false'}/tmem"
+    for cfg in range(1, 400):
+        if L.config_name(cfg) == want:
+            return cfg
+    raise AssertionError(want)
+
+
+@pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
+@pytest.mark.parametrize("group", [128, -1])
+@pytest.mark.parametrize("m,k,n", [(1, 1024, 512), (7, 2048, 448), (16, 1024, 1536), (20, 512, 256), (32, 4096, 832)])
+def test_tensor_memory_streaming_kernel(dtype, group, m, k, n):
+    """w4a16_decode_tc_kernel (decode_tc_kernel.cuh): dequantised fragments written from registers into tensor memory
+    as the A operand of tcgen05.mma, the token rows as the B operand, the accumulator in tensor memory.  Oracle-correct for
+    grouped and channelwise scales, ragged N (the last 256-column tile is partly out of range), split and whole columns
+    (contract-sized scratch), bit-identical run to run and under PDL, workspace returned zeroed."""
+    prob = mo.make_problem(m, k, n, group, dtype, seed=m * 3 + n)
+    c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, group, dtype)
+    cfg = tmem_config(dtype, m, group)
+    out1, _ = run_ours(prob, m, n, k, dtype, group=group, force_config=cfg)
+    out2, _ = run_ours(prob, m, n, k, dtype, group=group, force_config=cfg, pdl=True)
+    assert torch.equal(out1, out2)
+    st = mo.error_stats(t_load(out1, dtype), exact, dtype)
+    assert st["max_rel"] <= TOL_MAX_REL, st
+    out3, _ = run_ours(prob, m, n, k, dtype, group=group, force_config=cfg, contract=True)
+    st3 = mo.error_stats(t_load(out3, dtype), exact, dtype)
+    assert st3["max_rel"] <= TOL_MAX_REL, st3
+
+
+def test_tensor_memory_streaming_kernel_full_size_and_postops():
+    """the tensor-memory kernel at the full gate_up size against the default streaming kernel (same inputs: fp32
+    accumulation in both, only the summation order differs), with the epilogue's post-ops and the q/k/v split write"""
+    b = _b()
+    g = torch.Generator(device=DEV).manual_seed(11)
+    for m, k, n in [(16, 4096, 32768), (32, 4096, 4608)]:
+        qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=DEV, generator=g)
+        sc = (torch.rand((k // 128, n), device=DEV, generator=g) * 0.018 + 0.002).half()
+        a = torch.randn((m, k), device=DEV, generator=g).half()
+        res = torch.randn((m, n), device=DEV, generator=g).half()
+        bias = torch.randn((n,), device=DEV, generator=g).half()
+        ws, c_tmp = scratch(m, n, k)
+        cfg = tmem_config(mo.FP16, m, 128)
+        ref = b.gemm(a, qw, sc, ws, c_tmp, residual=res, bias=bias, out_scale=0.25)
+        out = b.gemm(a, qw, sc, ws, c_tmp, residual=res, bias=bias, out_scale=0.25, force_config=cfg)
+        torch.cuda.synchronize()
+        scale = float(ref.float().abs().mean())
+        assert float((out.float() - ref.float()).abs().max()) <= 1e-2 * scale
+        assert int(ws.abs().max()) == 0
+    qa, qb = 4096, 256
+    plain = b.gemm(a, qw, sc, ws, c_tmp, force_config=cfg)
+    split = b.gemm(a, qw, sc, ws, c_tmp, force_config=cfg, qkv_split=(qa, qb))
+    torch.cuda.synchronize()
+    flat = split.reshape(-1)
+    assert torch.equal(flat[: m * qa].view(m, qa), plain[:, :qa])
+    assert torch.equal(flat[m * qa: m * (qa + qb)].view(m, qb), plain[:, qa:qa + qb])
+    assert torch.equal(flat[m * (qa + qb):].view(m, qb), plain[:, qa + qb:])
 
 
 @pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
