@@ -304,8 +304,12 @@ __device__ __forceinline__ void finish_segment(const DecodeArgs& p, const float*
   // ---- last arriver: every other partial is visible (released before the other tickets, acquired with ours) ----
   if (tid == 0) *cs.counter = 0;      // all sharers have drawn: the workspace goes back to zero (reference contract)
   const int np1 = cs.nparts - 1;
-  if (stage == nullptr || cap < np1 * (GATED ? RI : 1)) {
-    // straight from L2 (the flusher warp drew the last ticket: rare, its shared memory is live)
+  // few loads per thread (decode widths: M x TN / 4 items x the other sharers over the group's threads): straight from L2
+  // into registers — every load is in flight at once anyway, and the shared-memory staging round (cp.async, wait, two
+  // barriers) is pure latency on the kernel's critical tail
+  const bool direct = items * np1 <= 8 * nthr;
+  if (stage == nullptr || direct || cap < np1 * (GATED ? RI : 1)) {
+    // (also when the flusher warp drew the last ticket: its shared memory is live)
     auto sum_item = [&](int item) {
       float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int sl = 0; sl < cs.nparts; ++sl) {   // slot order: bit-deterministic
