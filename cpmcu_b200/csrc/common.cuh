@@ -324,6 +324,20 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
       : "r"(taddr)
       : "memory");
 }
+// 32 lanes x N consecutive fp32 columns, N in {8, 16, 32}
+template <int N>
+__device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t (&v)[N]);
+template <>
+__device__ __forceinline__ void tmem_ld_cols<8>(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr)
+               : "memory");
+}
+template <>
+__device__ __forceinline__ void tmem_ld_cols<16>(uint32_t taddr, uint32_t (&v)[16]) { tmem_ld_32x16(taddr, v); }
+template <>
+__device__ __forceinline__ void tmem_ld_cols<32>(uint32_t taddr, uint32_t (&v)[32]) { tmem_ld_32x32(taddr, v); }
 // ---- A operand in TENSOR MEMORY, written from registers (tools/probe_tmem_a.cu pins the layout on B200) ----
 // One 16-row x 16-k block of a 16-bit A operand in the mma.sync fragment layout: thread (g = lane / 4, t = lane % 4)
 // passes {(row g, k 2t..2t+1), (row g + 8, same k), (row g, k 2t+8..2t+9), (row g + 8, same k)} — exactly

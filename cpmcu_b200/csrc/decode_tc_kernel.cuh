@@ -28,9 +28,12 @@
 
 namespace b200 {
 
-template <typename T, int NT, bool GROUPED>
+template <typename T, int NT, int CH, bool GROUPED>
 struct DecodeTcCfg {
-  using Base = DecodeCfg<T, NT, 4, 8, 8, 5, GROUPED>;
+  static constexpr int KROWS = CH == 4 ? 8 : 16;    // 256 columns x 128 k, or 128 columns x 256 k per stage (16 KB of int4 both)
+  using Base = DecodeCfg<T, NT, CH, KROWS, 8, 5, GROUPED>;
+  static constexpr int SUBS = CH / 2;                // 128-column UMMA halves of the tile
+  static constexpr int HALVES = KROWS / 4;           // hand-over units of 4 k16-rows per stage
   static constexpr int NROWS = NT * 8;               // token rows = UMMA N (16 or 32)
   static constexpr int WARPS = 8;
   static constexpr int THREADS = WARPS * 32 + 96;    // + producer, flusher, issuer
@@ -38,20 +41,22 @@ struct DecodeTcCfg {
   static constexpr int OFF_SLOT = OFF_XBAR + 6 * 8;
   static constexpr int SMEM_BYTES = OFF_SLOT + 16;
   static constexpr int TMEM_COLS = 256;
-  static constexpr int TM_A = 64;                     // first column of the A ring
+  static constexpr int TM_A = SUBS * NROWS > 64 ? SUBS * NROWS : 64;   // first column of the A ring
+  static constexpr int A_BUF = SUBS * 32;             // columns of one A buffer (4 k16-rows x 8 columns per half)
   static_assert(NT == 2 || NT == 4, "token rows: 16 or 32 (UMMA N is a multiple of 16)");
-  static_assert(Base::KB == 128 && Base::SG == 1 && Base::KC == 2, "one scale group and two 64-k token boxes per stage");
+  static_assert(CH == 2 || CH == 4, "tile: 128 or 256 columns");
+  static_assert(Base::KC == HALVES && TM_A + 2 * A_BUF <= TMEM_COLS, "one 64-k token box per hand-over unit; TMEM budget");
 };
 
-template <typename T, int NT, bool GROUPED>
-__global__ void __launch_bounds__(DecodeTcCfg<T, NT, GROUPED>::THREADS, 2)
+template <typename T, int NT, int CH, bool GROUPED>
+__global__ void __launch_bounds__(DecodeTcCfg<T, NT, CH, GROUPED>::THREADS, 2)
 w4a16_decode_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_s,
                        const __grid_constant__ CUtensorMap tm_a, const DecodeArgs p) {
-  using TC = DecodeTcCfg<T, NT, GROUPED>;
+  using TC = DecodeTcCfg<T, NT, CH, GROUPED>;
   using Cfg = typename TC::Base;
   constexpr int TN = Cfg::TN, TNP = Cfg::TNP, NS = Cfg::NSTAGE, WARPS = TC::WARPS, NROWS = TC::NROWS;
   constexpr int NCONS = WARPS * 32;
-  constexpr int CHUNKS = 4, KROWS = 8, KB = Cfg::KB;
+  constexpr int CHUNKS = CH, KROWS = TC::KROWS, KB = Cfg::KB, SUBS = TC::SUBS, HALVES = TC::HALVES;
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;
@@ -82,7 +87,7 @@ w4a16_decode_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_co
     mbar_init(bar_red_empty, 1);
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
-      mbar_init(bar_a_full + 8 * b, WARPS);
+      mbar_init(bar_a_full + 8 * b, CH == 4 ? WARPS : WARPS / 2);   // the warps that write a hand-over unit
       mbar_init(bar_a_empty + 8 * b, 1);
     }
     mbar_init(bar_d_full, 1);
@@ -187,16 +192,17 @@ w4a16_decode_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_co
     const uint32_t idesc = umma_idesc_f16<T>(128, NROWS);
     const uint32_t b_lo0 = (((sbase + Cfg::ST_A) & 0x3FFFFu) >> 4) | (1u << 16);
     const SegWalk walk(u0, u1, p.kblks);
-    uint32_t s = 0, ph = 0, hs = 0;
+    uint32_t s = 0, ph = 0, it = 0;
     for (int si = 0; si < walk.nseg; ++si) {
       int seg_c, seg_b0, seg_b1;
       walk.get(si, seg_c, seg_b0, seg_b1);
-      for (int ub = seg_b0; ub < seg_b1; ++ub) {
+      for (int ub = seg_b0; ub < seg_b1; ++ub, ++it) {
         mbar_wait(bar_full + 8 * s, ph);   // the token rows of the stage have landed
 #pragma unroll
-        for (int h = 0; h < 2; ++h, ++hs) {
-          const uint32_t b = hs & 1u;
-          mbar_wait(bar_a_full + 8 * b, (hs >> 1) & 1u);
+        for (int h = 0; h < HALVES; ++h) {
+          const uint32_t b = h & 1;
+          const uint32_t use = it * (HALVES / 2) + (h >> 1);   // how often buffer b has been filled before
+          mbar_wait(bar_a_full + 8 * b, use & 1u);
           tc_fence_after();
           if (elect_one()) {
             const uint32_t b_lo = b_lo0 + s * (Cfg::STAGE_BYTES >> 4) + h * (Cfg::A_SUB >> 4);
@@ -205,11 +211,11 @@ w4a16_decode_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_co
               const uint64_t bdesc = (static_cast<uint64_t>(kDescHi) << 32) | (b_lo + r * 2);
               const uint32_t accum = (ub != seg_b0 || h != 0 || r != 0) ? 1u : 0u;
 #pragma unroll
-              for (int sub = 0; sub < 2; ++sub)
-                tc_mma_f16_ts(tm + sub * NROWS, tm + TC::TM_A + b * 64 + sub * 32 + r * 8, bdesc, idesc, accum);
+              for (int sub = 0; sub < SUBS; ++sub)
+                tc_mma_f16_ts(tm + sub * NROWS, tm + TC::TM_A + b * TC::A_BUF + sub * 32 + r * 8, bdesc, idesc, accum);
             }
             tc_commit(bar_a_empty + 8 * b);
-            if (h == 1) {
+            if (h == HALVES - 1) {
               tc_commit(bar_empty + 8 * s);
               if (ub == seg_b1 - 1) tc_commit(bar_d_full);
             }
@@ -226,22 +232,27 @@ w4a16_decode_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_co
   }
 
   // ====================================== dequantisers ======================================
-  const int q = warp & 3;    // TMEM lane quarter this warp may access
-  const int sb = warp >> 2;  // 128-column half of the tile
+  // warp w: TMEM lane quarter q = w % 4; grp = w / 4 is the 128-column half of a 256-column tile (CH == 4: every
+  // hand-over unit of the stage) or, for the 128-column tile, the parity of the hand-over units it converts (CH == 2)
+  const int q = warp & 3;
+  const int grp = warp >> 2;
   const int g = lane >> 2;
-  const int chunk = 2 * sb + (q >> 1);
+  const int sub = CH == 4 ? grp : 0;
+  const int chunk = 2 * sub + (q >> 1);
   const int jb = 2 * (q & 1);   // first of the two words (16-column blocks) of the chunk this warp converts
   // per-lane offsets inside a stage block: 8 bytes (words jb, jb + 1) of k16-row r's 512-byte block of `chunk`; the
   // matching two scale words (word j = {s[16j + g], s[16j + g + 8]}, common.cuh)
   const uint32_t q_off = Cfg::ST_W + static_cast<uint32_t>(chunk * 512 + lane * 16 + jb * 4);
   const uint32_t sc_off = Cfg::ST_S + static_cast<uint32_t>(chunk * 128 + g * 16 + jb * 4);
-  // tensor-memory address of this warp's A rows: lane 32q (+ 16 for the second word), column TM_A + 32 * sb
-  const uint32_t ta0 = tm + (static_cast<uint32_t>(32 * q) << 16) + TC::TM_A + 32 * sb;
-  const uint32_t td = tm + (static_cast<uint32_t>(32 * q) << 16) + sb * NROWS;
+  // tensor-memory address of this warp's A rows: lane 32q (+ 16 for the second word), column TM_A + 32 * sub
+  const uint32_t ta0 = tm + (static_cast<uint32_t>(32 * q) << 16) + TC::TM_A + 32 * sub;
+  constexpr int MYH = CH == 4 ? HALVES : HALVES / 2;   // hand-over units this warp converts per stage
+  constexpr int DCOLS = CH == 4 ? NROWS : NROWS / 2;   // accumulator columns (tokens) this warp reads back
+  const uint32_t td = tm + (static_cast<uint32_t>(32 * q) << 16) + (CH == 4 ? sub * NROWS : grp * DCOLS);
 
   const SegWalk walk(u0, u1, p.kblks);
   int s = 0;
-  uint32_t ph = 0, hs = 0;
+  uint32_t ph = 0, it = 0;
   uint32_t stg = sbase, bfull = bar_full, bempty = bar_empty;
 
   mbar_wait_backoff(bar_full, 0, 64);  // under PDL this first wait spans the tail of the previous kernel
@@ -250,26 +261,32 @@ w4a16_decode_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_co
   for (int si = 0; si < walk.nseg; ++si) {
     int seg_c, seg_b0, seg_b1;
     walk.get(si, seg_c, seg_b0, seg_b1);
-    for (int ub = seg_b0; ub < seg_b1; ++ub) {
+    for (int ub = seg_b0; ub < seg_b1; ++ub, ++it) {
       mbar_wait(bfull, ph);
-      uint32_t sc[2] = {0u, 0u};
-      if (GROUPED) {
-        const uint2 sv = lds64(stg + sc_off);
-        sc[0] = sv.x;
-        sc[1] = sv.y;
+      uint2 qw[MYH][4];
+#pragma unroll
+      for (int i = 0; i < MYH; ++i) {
+        const int h = CH == 4 ? i : 2 * i + grp;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) qw[i][r] = lds64(stg + q_off + (4 * h + r) * (CHUNKS * 512));
       }
-      uint2 qw[8];
 #pragma unroll
-      for (int r = 0; r < 8; ++r) qw[r] = lds64(stg + q_off + r * (CHUNKS * 512));
-#pragma unroll
-      for (int h = 0; h < 2; ++h, ++hs) {
-        const uint32_t b = hs & 1u;
-        mbar_wait(bar_a_empty + 8 * b, ((hs >> 1) & 1u) ^ 1u);   // the UMMAs that read this buffer two half-stages ago are done
+      for (int i = 0; i < MYH; ++i) {
+        const int h = CH == 4 ? i : 2 * i + grp;     // hand-over unit: k16-rows 4h .. 4h + 3
+        const uint32_t b = h & 1;
+        const uint32_t use = it * (HALVES / 2) + (h >> 1);
+        uint32_t sc[2] = {0u, 0u};
+        if (GROUPED) {   // rows 8.. of a 256-k stage belong to the next scale group
+          const uint2 sv = lds64(stg + sc_off + (Cfg::SG > 1 ? (h >> 1) * (TN * 2) : 0));
+          sc[0] = sv.x;
+          sc[1] = sv.y;
+        }
+        mbar_wait(bar_a_empty + 8 * b, (use & 1u) ^ 1u);   // the UMMAs that read this buffer last time are done
         tc_fence_after();
-        const uint32_t ta = ta0 + b * 64;
+        const uint32_t ta = ta0 + b * TC::A_BUF;
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-          const uint32_t two[2] = {qw[4 * h + r].x, qw[4 * h + r].y};
+          const uint32_t two[2] = {qw[i][r].x, qw[i][r].y};
 #pragma unroll
           for (int jj = 0; jj < 2; ++jj) {
             uint32_t w[4];
@@ -299,17 +316,14 @@ w4a16_decode_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_co
     mbar_wait(bar_d_full, static_cast<uint32_t>(si) & 1u);            // every UMMA of the segment has completed
     tc_fence_after();
     {
-      uint32_t v[NROWS];
-      if (NROWS == 16) {
-        tmem_ld_32x16(td, reinterpret_cast<uint32_t(&)[16]>(v));
-      } else {
-        tmem_ld_32x32(td, reinterpret_cast<uint32_t(&)[32]>(v));
-      }
+      uint32_t v[DCOLS];
+      tmem_ld_cols<DCOLS>(td, v);
       tmem_ld_wait();
-      const int n = 128 * sb + 32 * q + lane;
+      const int n = 128 * sub + 32 * q + lane;
+      const int tok0 = CH == 4 ? 0 : grp * DCOLS;
 #pragma unroll
-      for (int i = 0; i < NROWS; ++i)
-        if (i < p.m) red[i * TNP + n] = __uint_as_float(v[i]);
+      for (int i = 0; i < DCOLS; ++i)
+        if (tok0 + i < p.m) red[(tok0 + i) * TNP + n] = __uint_as_float(v[i]);
     }
     tc_fence_before();
     if (si == walk.nseg - 1) {

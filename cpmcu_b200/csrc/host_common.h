@@ -49,13 +49,13 @@ unsigned long long* debug_next_slot();
 
 // ---- streaming (decode) regime: geometries of w4a16_decode_kernel and the launch plan ----
 struct DecodeGeom { int chunks, krows, warps, stages; };
-constexpr int kGeoms = 8;
+constexpr int kGeoms = 9;
 // 0: the default (256 columns x 128 k per stage, 8 consumer warps)      1: the same tile with 64-k stages (K % 128 != 0)
 // 2: 64 columns x 512 k, for whole-column launches                     3, 4: 16 consumer warps (more warps per scheduler)
 // 5: 128 columns x 256 k                                              6: the default tile with a 10-deep ring (one CTA per SM)
-// 7: the default tile on tcgen05 / tensor memory (w4a16_decode_tc_kernel, decode_tc_kernel.cuh); token rows 16 or 32
-constexpr DecodeGeom kGeom[kGeoms] = {{4, 8, 8, 5}, {4, 4, 8, 8}, {1, 32, 8, 4}, {4, 8, 16, 5}, {4, 16, 16, 3}, {2, 16, 8, 5}, {4, 8, 8, 10}, {4, 8, 8, 5}};
-constexpr int kTcGeom = 7;
+// 7, 8: tiles 0 and 5 on tcgen05 / tensor memory (w4a16_decode_tc_kernel, decode_tc_kernel.cuh); token rows 16 or 32
+constexpr DecodeGeom kGeom[kGeoms] = {{4, 8, 8, 5}, {4, 4, 8, 8}, {1, 32, 8, 4}, {4, 8, 16, 5}, {4, 16, 16, 3}, {2, 16, 8, 5}, {4, 8, 8, 10}, {4, 8, 8, 5}, {2, 16, 8, 5}};
+constexpr int kTcGeom = 7, kTcGeom2 = 8;   // tensor-memory kernel: 256- and 128-column tiles
 constexpr int kWholeColGeom = 2;
 
 // Upper bound on the number of CTAs whose unit ranges intersect one column of `kblks` units when

@@ -67,7 +67,7 @@ struct PrefillCfg {
   static constexpr int OFF_Q = OFF_W + STAGES * W_STAGE;
   static constexpr int OFF_S = OFF_Q + QSTAGES * Q_STAGE;
   static constexpr int OFF_BAR = (OFF_S + QSTAGES * S_STAGE + 127) / 128 * 128;
-  static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4;
+  static constexpr int NBARS = 3 * STAGES + 2 * QSTAGES + 4 + (PAIR ? STAGES : 0);
   static constexpr int SMEM_BYTES = OFF_BAR + NBARS * 8 + 16;
   static constexpr int THREADS = (7 + DW) * 32;
   static_assert(DWG % CHUNKS == 0 && WPC >= 1 && 4 % WPC == 0, "dequant warp layout");
@@ -101,6 +101,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
   const uint32_t bar_q_empty = bar_q_full + QSTAGES * 8;
   const uint32_t bar_acc_full = bar_q_empty + QSTAGES * 8;
   const uint32_t bar_acc_empty = bar_acc_full + 2 * 8;
+  const uint32_t bar_w_peer = bar_acc_empty + 2 * 8;   // PAIR, leader's copy: the peer CTA's half of the W stage is written
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + Cfg::OFF_BAR + Cfg::NBARS * 8);
 
   // warp index through a shuffle: provably warp-uniform for ptxas, so the role branches are uniform branches and the
@@ -112,8 +113,9 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(bar_a_full + 8 * s, 1);
-      mbar_init(bar_w_full + 8 * s, PAIR ? 2 * Cfg::DWG : Cfg::DWG);   // PAIR: the peer's dequantisers arrive here too
+      mbar_init(bar_w_full + 8 * s, Cfg::DWG);
       mbar_init(bar_consumed + 8 * s, 1);
+      if (PAIR) mbar_init(bar_w_peer + 8 * s, 1);
     }
 #pragma unroll
     for (int s = 0; s < QSTAGES; ++s) {
@@ -236,6 +238,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       for (int kb = kb_lo; kb < kb_hi; ++kb) {
         mbar_wait(bar_a_full + 8 * s, ph);
         mbar_wait(bar_w_full + 8 * s, ph);
+        if (PAIR) mbar_wait(bar_w_peer + 8 * s, ph);
         tc_fence_after();
         if (elect_one()) {
           const uint32_t a_lo = a_lo0 + s * (Cfg::A_STAGE >> 4);
@@ -264,6 +267,28 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
           s = 0;
           ph ^= 1u;
         }
+      }
+    }
+  } else if (PAIR && warp == 5) {
+    // ============ PAIR, peer CTA: forwards "my half of W stage s is written" to the leader ============
+    // The dequantisers arrive on their OWN CTA's w_full — a local arrive travels the same shared-memory pipeline as
+    // their stmatrix stores, so the phase cannot complete before the stores have landed — and this otherwise idle warp
+    // turns each completed phase into one plain remote arrive on the leader's w_peer.  Arriving remotely straight
+    // from the dequant warps was a race: the remote arrive takes the SM-to-SM network and, about once in 2700
+    // launches, reached the leader before the peer's last stores had reached its shared memory, so the pair's UMMA
+    // read a stale half-stage (profiles/r02/o_pair_tile_race.txt); the `.release.cluster` form is safe but puts a
+    // ~1 us cluster-scope fence in front of every arrive.
+    int my_tiles = 0;
+    for (int tile = tile_begin; tile < total_tiles; tile += tile_step) ++my_tiles;
+    const int total_its = my_tiles * (kb_hi - kb_lo);
+    uint32_t s = 0, ph = 0;
+    for (int it = 0; it < total_its; ++it) {
+      mbar_wait(bar_w_full + 8 * s, ph);
+      if (elect_one()) mbar_arrive_leader(bar_w_peer + 8 * s);
+      __syncwarp();
+      if (++s == STAGES) {
+        s = 0;
+        ph ^= 1u;
       }
     }
   } else if (warp >= 7) {
@@ -301,6 +326,20 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       for (int i = 0; i < Cfg::RPW; ++i)
         q[i] = lds128(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE + q_lane + i * (Cfg::WPC * CHUNKS * 512));
       mbar_wait(bar_consumed + 8 * s, wph);  // W slot drained by the tensor core
+      if (PAIR) {
+        // CTA pairs: one more k-block of slack.  The multicast commit that frees slot s arrives in BOTH CTAs at one
+        // point in time while the two tensor cores do not finish reading their shared memory at the same instant; a
+        // dequantiser that rewrites its W slot right behind that arrive corrupted a half-stage about once in 2700
+        // launches (profiles/r02/o_pair_tile_race.txt; the TMA refill of the token slot is a microsecond later and
+        // never showed it).  The UMMAs of a tensor core complete in order, so once the NEXT k-block's commit has
+        // arrived this slot's reads are over on both SMs (two k-blocks: one left 1 mismatch in 32000 launches).
+        constexpr int kSlack = 2;
+#pragma unroll
+        for (int d = 1; d <= kSlack; ++d) {
+          const int it1 = it + d - STAGES;   // the d-th k-block after the one that last used slot s
+          if (it1 >= 0 && it1 < total_its) mbar_wait(bar_consumed + 8 * (it1 % STAGES), (it1 / STAGES) & 1);
+        }
+      }
       const uint32_t w_addr = sbase + Cfg::OFF_W + s * Cfg::W_STAGE;
 #pragma unroll
         for (int i = 0; i < Cfg::RPW; ++i) {
@@ -320,10 +359,7 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       // shared-memory loads are then complete by data dependence, not by an assumption about issue order
       // (releasing right after ISSUING the loads was the round-1 split-K race)
       if (lane == 0) mbar_arrive(bar_q_empty + 8 * sq);
-      if (lane == 0) {
-        if (PAIR) mbar_arrive_leader(bar_w_full + 8 * s);   // the leader's issuer waits for both CTAs' halves of the W operand
-        else mbar_arrive(bar_w_full + 8 * s);
-      }
+      if (lane == 0) mbar_arrive(bar_w_full + 8 * s);   // PAIR, peer CTA: its warp 5 forwards the completed phase to the leader
       sq += Cfg::DGROUPS;
       if (sq >= QSTAGES) { sq -= QSTAGES; qph ^= 1u; }
       s += Cfg::DGROUPS;

@@ -202,7 +202,7 @@ bool geom_fits(int geo, int n, int k, bool gated) {
 // streams the same number of bytes; split columns are reduced through fp32 slots in c_tmp) whenever the
 // slots fit; otherwise fewer CTAs (fewer sharers per column) or whole columns per CTA (no scratch at all),
 // whichever leaves the shorter critical path.  geom < 0: the default geometry for the shape.
-DecodePlan plan_decode(int mm, int n, int k, int geom, long long capacity, bool gated) {
+DecodePlan plan_decode(int mm, int n, int k, int geom, long long capacity, bool gated, bool tmem_ok = true) {
   const int sms = sm_count();
   auto dims = [&](int geo, DecodePlan* pl) {
     const int tn = kGeom[geo].chunks * 64, kb = kGeom[geo].krows * 16;
@@ -254,8 +254,12 @@ DecodePlan plan_decode(int mm, int n, int k, int geom, long long capacity, bool 
   // shape (qkv, o, down) is shared by 8+ CTAs and the last arriver of a column pulls 8 x M x 1 KB: the 128-column x 256-k
   // stage halves both.  ONE geometry per token-block width for every shape: alternating between two kernel functions
   // inside a layer costs more than the better per-shape choice gains (M = 16: 74 us per layer mixed, 67 us uniform).
+  // For M > 16 the same 128-column x 256-k tile runs on tcgen05 with the A operand in tensor memory (geometry 8,
+  // decode_tc_kernel.cuh) unless the launch needs the fused all-reduce: mma.sync costs 16-17 cycles per word per 8 tokens,
+  // the tensor-memory route does not depend on M (MiniCPM4-8B layer at M = 32: 82 vs 95 us; at M = 16 it is 2 % ahead
+  // on the 8B shapes and 6 % behind on the Llama-70B ones, so M <= 16 stays on mma.sync; profiles/r02/n_tmem_*).
   int g0 = (k % 128) == 0 ? 0 : 1;
-  if (geom < 0 && !gated && mm > 8 && (k % 256) == 0) g0 = 5;
+  if (geom < 0 && !gated && mm > 8 && (k % 256) == 0) g0 = (tmem_ok && mm > 16) ? kTcGeom2 : 5;
   if (geom >= 0) g0 = geom;
   DecodePlan best;
   bool have = stream_k(g0, &best);
@@ -293,7 +297,7 @@ const char* decode_name(int id) {
   decode_from_id(id, &dtype, &nt, &grouped, &geom);
   snprintf(buf, sizeof(buf), "%s/nt%d/tn%dx64/kb%dx16/w%d/s%d/%s%s", dtype == 0 ? "__half" : "__nv_bfloat16", nt,
            kGeom[geom].chunks, kGeom[geom].krows, kGeom[geom].warps, kGeom[geom].stages, grouped ? "true" : "false",
-           geom == kTcGeom ? "/tmem" : "");
+           geom >= kTcGeom ? "/tmem" : "");
   return buf;
 }
 
@@ -555,7 +559,7 @@ static int gemm_impl(const void* a, const int32_t* qweight, const void* scales, 
     s.c = static_cast<char*>(c) + static_cast<size_t>(m0) * (gated ? n / 2 : n) * esz;
     s.residual = g.residual ? static_cast<const char*>(g.residual) + static_cast<size_t>(m0) * n * esz : nullptr;
     s.m = mm;
-    const DecodePlan pl = plan_decode(mm, s.n, s.k, geom, capacity, gated);
+    const DecodePlan pl = plan_decode(mm, s.n, s.k, geom, capacity, gated, /*tmem_ok=*/g.ar_world <= 1);
     const int nt = forced > 0 ? (1 << (((forced - 1) / kGeoms) % 3)) : nt_for_m(mm);
     if (int rc = (dtype == 0 ? launch_decode_fp16(s, pl, nt) : launch_decode_bf16(s, pl, nt))) return rc;
   }

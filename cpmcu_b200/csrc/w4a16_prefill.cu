@@ -159,7 +159,7 @@ int launch_tile(const GemmCall& g, int tile, int S, int* query) {
     case 3: return launch_one<T, 1, 128, 6, 6, 8, GROUPED, false>(g, 1, query);
     case 4: return launch_one<T, 1, 64, 2, 10, 8, GROUPED, true>(g, S, query);
     case 5: return launch_one<T, 1, 128, 2, 8, 8, GROUPED, true>(g, S, query);
-    case 6: return launch_one<T, 1, 256, 5, 5, 8, GROUPED, false, true>(g, 1, query);
+    case 6: return launch_one<T, 1, 256, 6, 4, 8, GROUPED, false, true>(g, 1, query);
   }
   return fail(B200_W4A16_EINVAL, "tcgen05 tile id %d out of range", tile);
 }

@@ -208,11 +208,14 @@ def test_all_decode_configs_agree():
     assert seen >= 5
 
 
-def tmem_config(dtype, m, group):
-    """force_config id of the tensor-memory streaming kernel (geometry 7, '/tmem') for this dtype / width / scale kind"""
+TMEM_TILES = ["tn4x64/kb8x16", "tn2x64/kb16x16"]   # geometries 7 and 8: 256 columns x 128 k, 128 columns x 256 k
+
+
+def tmem_config(dtype, m, group, tile=TMEM_TILES[0]):
+    """force_config id of the tensor-memory streaming kernel (names ending in '/tmem') for this dtype / width / scale kind"""
     from cpmcu_b200 import capi as L
     nt = 1 if m <= 8 else (2 if m <= 16 else 4)
-    want = f"{'__half' if dtype == mo.FP16 else '__nv_bfloat16'}/nt{nt}/tn4x64/kb8x16/w8/s5/{'true' if group != -1 else 'false'}/tmem"
+    want = f"{'__half' if dtype == mo.FP16 else '__nv_bfloat16'}/nt{nt}/{tile}/w8/s5/{'true' if group != -1 else 'false'}/tmem"
     for cfg in range(1, 400):
         if L.config_name(cfg) == want:
             return cfg
@@ -221,15 +224,16 @@ def tmem_config(dtype, m, group):
 
 @pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
 @pytest.mark.parametrize("group", [128, -1])
+@pytest.mark.parametrize("tile", TMEM_TILES)
 @pytest.mark.parametrize("m,k,n", [(1, 1024, 512), (7, 2048, 448), (16, 1024, 1536), (20, 512, 256), (32, 4096, 832)])
-def test_tensor_memory_streaming_kernel(dtype, group, m, k, n):
+def test_tensor_memory_streaming_kernel(dtype, group, m, k, n, tile):
     """w4a16_decode_tc_kernel (decode_tc_kernel.cuh): dequantised fragments written from registers into tensor memory
     as the A operand of tcgen05.mma, the token rows as the B operand, the accumulator in tensor memory.  Oracle-correct for
-    grouped and channelwise scales, ragged N (the last 256-column tile is partly out of range), split and whole columns
+    grouped and channelwise scales, both tile shapes, ragged N (the last tile is partly out of range), split and whole columns
     (contract-sized scratch), bit-identical run to run and under PDL, workspace returned zeroed."""
     prob = mo.make_problem(m, k, n, group, dtype, seed=m * 3 + n)
     c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, group, dtype)
-    cfg = tmem_config(dtype, m, group)
+    cfg = tmem_config(dtype, m, group, tile)
     out1, _ = run_ours(prob, m, n, k, dtype, group=group, force_config=cfg)
     out2, _ = run_ours(prob, m, n, k, dtype, group=group, force_config=cfg, pdl=True)
     assert torch.equal(out1, out2)
@@ -241,9 +245,10 @@ def test_tensor_memory_streaming_kernel(dtype, group, m, k, n):
 
 
 def test_tensor_memory_streaming_kernel_full_size_and_postops():
-    """the tensor-memory kernel at the full gate_up size against the default streaming kernel (same inputs: fp32
+    """the tensor-memory kernel at the full gate_up size against the mma.sync streaming kernel (same inputs: fp32
     accumulation in both, only the summation order differs), with the epilogue's post-ops and the q/k/v split write"""
     b = _b()
+    from cpmcu_b200 import capi as L
     g = torch.Generator(device=DEV).manual_seed(11)
     for m, k, n in [(16, 4096, 32768), (32, 4096, 4608)]:
         qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=DEV, generator=g)
@@ -252,8 +257,10 @@ def test_tensor_memory_streaming_kernel_full_size_and_postops():
         res = torch.randn((m, n), device=DEV, generator=g).half()
         bias = torch.randn((n,), device=DEV, generator=g).half()
         ws, c_tmp = scratch(m, n, k)
-        cfg = tmem_config(mo.FP16, m, 128)
-        ref = b.gemm(a, qw, sc, ws, c_tmp, residual=res, bias=bias, out_scale=0.25)
+        cfg = tmem_config(mo.FP16, m, 128, TMEM_TILES[1])
+        assert "tmem" not in L.config_name(1)
+        ref = b.gemm(a, qw, sc, ws, c_tmp, residual=res, bias=bias, out_scale=0.25,
+                     force_config=next(c for c in range(1, 400) if L.config_name(c) == f"__half/nt{2 if m <= 16 else 4}/tn2x64/kb16x16/w8/s5/true"))
         out = b.gemm(a, qw, sc, ws, c_tmp, residual=res, bias=bias, out_scale=0.25, force_config=cfg)
         torch.cuda.synchronize()
         scale = float(ref.float().abs().mean())
@@ -426,6 +433,16 @@ def test_out_scale_postop(tdt, m, force):
     assert st["max_rel"] <= TOL_MAX_REL, st
 
 
+def gated_family_config(tdt, m, k):
+    """the plain streaming configuration whose arithmetic the fused-activation kernel shares (geometry 0, or 1 when
+    K is not a multiple of 128): the mma.sync kernel with the 256-column tile"""
+    from cpmcu_b200 import capi as L
+    nt = 1 if m <= 8 else (2 if m <= 16 else 4)
+    tile = "tn4x64/kb8x16/w8/s5" if k % 128 == 0 else "tn4x64/kb4x16/w8/s8"
+    want = f"{'__half' if tdt == torch.float16 else '__nv_bfloat16'}/nt{nt}/{tile}/true"
+    return next(c for c in range(1, 400) if L.config_name(c) == want)
+
+
 @pytest.mark.parametrize("tdt", [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize("m", [1, 5, 8, 9, 16, 24, 32])
 @pytest.mark.parametrize("k,inter", [(512, 384), (128, 256), (2048, 1024)])
@@ -440,7 +457,7 @@ def test_gated_silu_fused(tdt, m, k, inter):
     prob = mo.make_problem(m, k, n, 128, dtype, seed=41 + m)
     a, qw, sc = t_store(prob["a"], dtype), torch.from_numpy(prob["qweight"]).to(DEV), t_store(prob["scales_marlin"], dtype)
     ws, c_tmp = scratch(m, n, k)
-    plain = b.gemm(a, qw, sc, ws, c_tmp)
+    plain = b.gemm(a, qw, sc, ws, c_tmp, force_config=gated_family_config(tdt, m, k))
     got = b.gemm(a, qw, sc, ws, c_tmp, gated_silu=True)
     torch.cuda.synchronize()
     assert got.shape == (m, inter)
@@ -467,7 +484,7 @@ def test_gated_silu_full_size(m):
     sc = (torch.rand((k // 128, n), device=DEV, generator=g) * 0.018 + 0.002).half()
     a = (torch.randn((m, k), device=DEV, generator=g) * 0.1).half()
     ws, c_tmp = scratch(m, n, k)
-    plain = b.gemm(a, qw, sc, ws, c_tmp)
+    plain = b.gemm(a, qw, sc, ws, c_tmp, force_config=gated_family_config(torch.float16, m, k))
     got = b.gemm(a, qw, sc, ws, c_tmp, gated_silu=True)
     torch.cuda.synchronize()
     gg, uu = plain[:, :inter].float(), plain[:, inter:].float()
@@ -669,8 +686,9 @@ def test_tcgen05_cta_pair_tile(dtype, m, k, n):
 def test_tcgen05_pair_tile_repeatable_under_pdl_chains(m):
     """the chunked-prefill chain as the operator runs it (auto-picked tiles: CTA pairs where a wave of pair tiles exists,
     single-CTA tiles elsewhere; PDL on, so every kernel's weight stream and dequantisers start under the previous
-    kernel's tail and cluster launches interleave with non-cluster ones): 40 passes over 2 layers x {qkv, o, gate_up,
-    down} at the MiniCPM4-8B sizes, every output bit-identical to the single-CTA tile's on every pass."""
+    kernel's tail and cluster launches interleave with non-cluster ones): 250 passes over 2 layers x {qkv, o, gate_up,
+    down} at the MiniCPM4-8B sizes, every output bit-identical to the single-CTA tile's on every pass.  (The pair tile
+    had a race that corrupted a half-stage once in ~2700 launches: profiles/r02/o_pair_tile_race*.txt.)"""
     b = _b()
     from cpmcu_b200 import capi as L
     shapes = [(4096, 4608), (4096, 4096), (4096, 32768), (16384, 4096)]
@@ -689,7 +707,7 @@ def test_tcgen05_pair_tile_repeatable_under_pdl_chains(m):
     refs = [b.gemm(a, qw, sc, ws, c_tmp, force_config=1002) for a, qw, sc, ws in w]
     outs = [torch.empty_like(r) for r in refs]
     torch.cuda.synchronize()
-    for rep in range(40):
+    for rep in range(250):
         for (a, qw, sc, ws), o in zip(w, outs):
             b.gemm(a, qw, sc, ws, c_tmp, out=o, pdl=True)
         torch.cuda.synchronize()

@@ -14,8 +14,11 @@ dev = "cuda"
 g = torch.Generator(device=dev).manual_seed(5)
 
 
+TILE = os.environ.get("TC_TILE", "tn4x64/kb8x16")
+
+
 def cfg_id(dtype, nt, grouped=True):
-    want = f"{'__half' if dtype == torch.float16 else '__nv_bfloat16'}/nt{nt}/tn4x64/kb8x16/w8/s5/{'true' if grouped else 'false'}/tmem"
+    want = f"{'__half' if dtype == torch.float16 else '__nv_bfloat16'}/nt{nt}/{TILE}/w8/s5/{'true' if grouped else 'false'}/tmem"
     for c in range(1, 200):
         if (L.config_name(c) or "") == want:
             return c
@@ -44,7 +47,7 @@ for dtype in (torch.float16, torch.bfloat16):
         err = float((out.float() - exact).abs().max() / exact.abs().mean())
         err_ref = float((ref.float() - exact).abs().max() / exact.abs().mean())
         same = bool(torch.equal(out, out2))
-        ok = err < 1e-2 and same and int(ws.abs().max()) == 0 and bool(torch.isfinite(out.float()).all())
+        ok = err <= err_ref * 1.05 + 1e-6 and same and int(ws.abs().max()) == 0 and bool(torch.isfinite(out.float()).all())
         bad += 0 if ok else 1
         print(f"{str(dtype)[6:]:9s} m={m:3d} k={k:5d} n={n:5d} cfg {cid:3d}: max rel err {err:.2e} (default kernel {err_ref:.2e}) repeatable {same} "
               f"{'ok' if ok else 'FAIL'}", flush=True)
