@@ -174,6 +174,13 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
           const int s = it % STAGES;
           mbar_wait_backoff(bar_consumed + 8 * s, ((it / STAGES) & 1) ^ 1, 32);
           if (PAIR) {
+            // the same two k-blocks of slack as the dequantisers take before they rewrite a W slot (see there): the
+            // refill lands a microsecond later and never showed the race, but the window is the same one
+#pragma unroll
+            for (int d = 1; d <= 2; ++d) {
+              const int it1 = it + d - STAGES;
+              if (it1 >= 0) mbar_wait_backoff(bar_consumed + 8 * (it1 % STAGES), (it1 / STAGES) & 1, 32);
+            }
             // tokens [m0 + rank * h, + h) with h = half of the tile's valid tokens rounded up to 16: the UMMA reads h rows
             // from each CTA, so accumulator column j is token m0 + j for ragged tiles too
             int vt = p.m - mt * BM;
