@@ -174,10 +174,11 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
           const int s = it % STAGES;
           mbar_wait_backoff(bar_consumed + 8 * s, ((it / STAGES) & 1) ^ 1, 32);
           if (PAIR) {
-            // the same two k-blocks of slack as the dequantisers take before they rewrite a W slot (see there): the
-            // refill lands a microsecond later and never showed the race, but the window is the same one
+            // one k-block of slack before the token slot is refilled (the dequantisers take two before they rewrite a
+            // W slot, see there): the TMA data lands >= 0.6 us after the request, which already covered the window — the
+            // refill never showed the race — and one k-block doubles that margin
 #pragma unroll
-            for (int d = 1; d <= 2; ++d) {
+            for (int d = 1; d <= 1; ++d) {
               const int it1 = it + d - STAGES;
               if (it1 >= 0) mbar_wait_backoff(bar_consumed + 8 * (it1 % STAGES), (it1 / STAGES) & 1, 32);
             }
