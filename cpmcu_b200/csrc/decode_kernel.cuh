@@ -635,6 +635,7 @@ w4a16_decode_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_const
   for (int si = 0; si < walk.nseg; ++si) {
    int seg_c, seg_b0, seg_b1;
    walk.get(si, seg_c, seg_b0, seg_b1);
+#pragma unroll 1
    for (int ub = seg_b0; ub < seg_b1; ++ub) {
     mbar_wait(bfull, ph);
 

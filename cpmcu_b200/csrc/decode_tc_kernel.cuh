@@ -196,7 +196,9 @@ w4a16_decode_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_co
     for (int si = 0; si < walk.nseg; ++si) {
       int seg_c, seg_b0, seg_b1;
       walk.get(si, seg_c, seg_b0, seg_b1);
-      for (int ub = seg_b0; ub < seg_b1; ++ub, ++it) {
+#pragma unroll 1
+  #pragma unroll 1
+    for (int ub = seg_b0; ub < seg_b1; ++ub, ++it) {
         mbar_wait(bar_full + 8 * s, ph);   // the token rows of the stage have landed
 #pragma unroll
         for (int h = 0; h < HALVES; ++h) {
@@ -261,6 +263,7 @@ w4a16_decode_tc_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_co
   for (int si = 0; si < walk.nseg; ++si) {
     int seg_c, seg_b0, seg_b1;
     walk.get(si, seg_c, seg_b0, seg_b1);
+#pragma unroll 1
     for (int ub = seg_b0; ub < seg_b1; ++ub, ++it) {
       mbar_wait(bfull, ph);
       uint2 qw[MYH][4];

@@ -259,7 +259,13 @@ DecodePlan plan_decode(int mm, int n, int k, int geom, long long capacity, bool 
   // the tensor-memory route does not depend on M (MiniCPM4-8B layer at M = 32: 82 vs 95 us; at M = 16 it is 2 % ahead
   // on the 8B shapes and 6 % behind on the Llama-70B ones, so M <= 16 stays on mma.sync; profiles/r02/n_tmem_*).
   int g0 = (k % 128) == 0 ? 0 : 1;
-  if (geom < 0 && !gated && mm > 8 && (k % 256) == 0) g0 = (tmem_ok && mm > 16) ? kTcGeom2 : 5;
+  if (geom < 0 && !gated && mm > 8 && (k % 256) == 0) {
+    static const int tmem_min_m = [] { const char* e = std::getenv("B200_W4A16_TMEM_MIN_M"); return e ? std::atoi(e) : 17; }();
+    // ONE tile for every shape of a layer: alternating the 256- and the 128-column tensor-memory tiles per shape is 4 %
+    // ahead at M = 16 in an 8-layer chain but not in the 32-layer bench graph, and far behind at M = 24 / 32
+    // (100 / 113 us against 82 uniform; profiles/r02/n_tmem_*).  B200_W4A16_TMEM_MIN_M moves the threshold (tuning).
+    g0 = (tmem_ok && mm >= tmem_min_m) ? kTcGeom2 : 5;
+  }
   if (geom >= 0) g0 = geom;
   DecodePlan best;
   bool have = stream_k(g0, &best);
