@@ -32,9 +32,6 @@ struct PrefillArgs {
   int m, n, k;
   int n_tiles, m_tiles, kblks;
   int qkv_a, qkv_b;      // > 0: q | k | v written split (out_offset, common.cuh)
-  int gated;             // 1: fused [gate | up] weight, c[M][N/2] = T(silu(gate) * up).  NSUB == 2 tiles only: sub-tile 0
-                         // holds 128 gate columns, sub-tile 1 the SAME 128 up columns (one 4-d TMA box, as in the streaming
-                         // kernel), so a thread finds both in its own TMEM lane; n_tiles counts 128-column output tiles
 };
 
 // PAIR: cta_group::2 — a cluster of two CTAs works on 256 weight columns x BM tokens: each CTA dequantises its own 128
@@ -216,21 +213,11 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
           mbar_wait_backoff(bar_q_empty + 8 * sq, ((it / QSTAGES) & 1) ^ 1, 32);
           mbar_arrive_expect_tx(bar_q_full + 8 * sq, Cfg::Q_STAGE + Cfg::S_STAGE);
           const int ch0 = PAIR ? (2 * nt + prank) * CHUNKS : nt * CHUNKS;   // PAIR: nt counts 256-column tiles
-          if (NSUB == 2 && !SPLIT && !PAIR && p.gated) {
-            // views int32 [K/16][2][I/64][128] and T [K/128][2][I/64][64]: box = 2 chunks of the gate half + the same 2
-            // chunks of the up half, landing exactly where the 3-d box puts 4 consecutive chunks
-            tma_load_4d(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE, &tm_w, bar_q_full + 8 * sq, 0, nt * 2, 0, kb * 4,
-                        kEvictNormal);
-            if (GROUPED)
-              tma_load_4d(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE, &tm_s, bar_q_full + 8 * sq, 0, nt * 2, 0, kb >> 1,
-                          kEvictLast);
-          } else {
           tma_load_3d(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE, &tm_w, bar_q_full + 8 * sq, 0, ch0,
                       kb * 4, SPLIT ? kEvictFirst : kEvictNormal);
           if (GROUPED)
             tma_load_3d(sbase + Cfg::OFF_S + sq * Cfg::S_STAGE, &tm_s, bar_q_full + 8 * sq, 0,
                         ch0, kb >> 1, kEvictLast);
-          }
         }
       }
     }
@@ -401,35 +388,6 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       vt = vt > BM ? BM : vt;
       T* cbase = reinterpret_cast<T*>(p.c);
       const T* rbase = reinterpret_cast<const T*>(p.residual);
-      if (NSUB == 2 && !SPLIT && !PAIR && p.gated) {
-        // fused FFN activation (gated_silu_interleaved, src/model/activation.cuh:7-18): TMEM lane = gate column j of
-        // sub-tile 0 AND up column j of sub-tile 1; g and u are rounded to T first (the reference's stored gate_up
-        // output), the activation uses __expf and the fast divide (the reference compiles with --use_fast_math)
-        const int half_n = p.n >> 1;
-        const int n_out = nt * 128 + qd * 32 + lane;
-        const bool nok = n_out < half_n;
-        T* cp = cbase + static_cast<size_t>(m0) * half_n + (nok ? n_out : 0);
-#pragma unroll 1
-        for (int c0 = 0; c0 < vt; c0 += 32) {
-          uint32_t vg[32], vu[32];
-          const uint32_t ta = tmem_base + (static_cast<uint32_t>(qd * 32) << 16) + acc * Cfg::ACC_COLS + c0;
-          tmem_ld_32x32(ta, vg);
-          tmem_ld_32x32(ta + BM, vu);
-          tmem_ld_wait();
-          if (nok) {
-            const int cnt = vt - c0;
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              if (i < cnt) {
-                const float gt = Elem<T>::to_float(Elem<T>::from_float(__uint_as_float(vg[i])));
-                const float ut = Elem<T>::to_float(Elem<T>::from_float(__uint_as_float(vu[i])));
-                const float sg = __fdividef(1.0f, 1.0f + __expf(-gt));
-                cp[static_cast<size_t>(c0 + i) * half_n] = Elem<T>::from_float(gt * sg * ut);
-              }
-            }
-          }
-        }
-      } else
 #pragma unroll 1
       for (int sub = 0; sub < NSUB; ++sub) {
         const int n = (PAIR ? (2 * nt + prank) * 128 : nt * Cfg::BN + sub * 128) + qd * 32 + lane;

@@ -472,10 +472,9 @@ static int gemm_impl(const void* a, const int32_t* qweight, const void* scales, 
   const int forced = opts ? opts->force_config : 0;
   const bool gated = opts && opts->gated_silu != 0;
   if (gated) {
-    // fused SiLU(gate) * up: the streaming kernel for decode / tree-verify widths, the 256-column whole-K tcgen05 tiles
-    // (gate and up halves as the two sub-tiles of one accumulator) beyond
-    if (forced >= kPrefillBase && forced != kPrefillBase && forced != kPrefillBase + 2)
-      return fail(B200_W4A16_EINVAL, "gated_silu on the tcgen05 path runs on the 256-column whole-K tiles (force_config %d or %d), got %d", kPrefillBase, kPrefillBase + 2, forced);
+    // fused SiLU(gate) * up: served by the persistent streaming kernel (decode / tree-verify widths)
+    if (m > kStreamMaxM || forced >= kPrefillBase)
+      return fail(B200_W4A16_EINVAL, "gated_silu is fused for M <= %d (got M = %lld, force_config %d)", kStreamMaxM, (long long)m, forced);
     if (group_size != 128 || (n % 256) != 0)
       return fail(B200_W4A16_EINVAL, "gated_silu needs group_size 128 and N (= 2 x intermediate) a multiple of 256, got N = %lld", (long long)n);
     if (opts->bias || opts->residual || opts->out_scale != 0.0f)

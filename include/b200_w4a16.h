@@ -62,10 +62,9 @@ typedef struct b200_w4a16_opts {
   /* 1 = the weight is the fused [gate | up] matrix (N = 2 x intermediate, gptq2marlin.py:162-230) and the
    * epilogue applies the FFN activation: c[M][N/2] = T(g * sigmoid(g) * u) with g, u the gate / up outputs
    * rounded to T first — gated_silu_interleaved (src/model/activation.cuh:7-18), the launch between
-   * gateup_proj and down_proj in w4a16_gptq_marlin_ffn.cuh:70-72.  Any M: the streaming kernel for M <= 32, the
-   * 256-column whole-K tcgen05 tiles beyond (gate half and the same columns of the up half as the two sub-tiles of
-   * one accumulator).  Needs group_size 128 and N % 256 == 0; does not combine with bias / residual / out_scale /
-   * act-order. */
+   * gateup_proj and down_proj in w4a16_gptq_marlin_ffn.cuh:70-72.  Streaming regime only (M <= 32); value
+   * error beyond, where the caller keeps the separate activation kernel.  Needs group_size 128 and
+   * N % 256 == 0; does not combine with bias / residual / out_scale / act-order. */
   int gated_silu;
   /* > 0: the weight is the fused q | k | v projection (N = qkv_q_dim + 2 * qkv_kv_dim) and `c` is written SPLIT,
    * [q: M x qkv_q_dim][k: M x qkv_kv_dim][v: M x qkv_kv_dim] — the layout the reference's `permute` launch produces

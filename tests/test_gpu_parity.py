@@ -276,6 +276,16 @@ def test_tensor_memory_streaming_kernel_full_size_and_postops():
     assert torch.equal(flat[m * (qa + qb):].view(m, qb), plain[:, qa + qb:])
 
 
+def test_disabled_tiles_are_rejected():
+    """the two single-CTA 256-column tiles failed intermittently in long PDL chains (profiles/r02/r_nsub2_tiles_stress.txt)
+    and are refused with a value error instead of being launched"""
+    b = _b()
+    prob = mo.make_problem(40, 256, 256, 128, mo.FP16, seed=1)
+    for cfg in (1001, 1003):
+        with pytest.raises(ValueError, match="disabled"):
+            run_ours(prob, 40, 256, 256, mo.FP16, force_config=cfg)
+
+
 @pytest.mark.parametrize("dtype", [mo.FP16, mo.BF16])
 def test_all_tcgen05_tiles_agree(dtype):
     """every tile shape of the tcgen05 kernel (force_config 1001..) gives the oracle's answer, bit-identical
@@ -285,8 +295,8 @@ def test_all_tcgen05_tiles_agree(dtype):
         prob = mo.make_problem(m, k, n, 128, dtype, seed=m)
         c, exact = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, dtype)
         outs = []
-        for cfg in range(1001, 1005):
-            assert L.config_name(cfg).startswith("tc/")
+        for cfg in (1002, 1004):   # 1001 / 1003 (256 columns per CTA) are disabled: DESIGN.md 6e
+            assert L.config_name(cfg).startswith("tc/bn128/")
             out1, _ = run_ours(prob, m, n, k, dtype, force_config=cfg)
             out2, _ = run_ours(prob, m, n, k, dtype, force_config=cfg)
             assert torch.equal(out1, out2), f"{L.config_name(cfg)}: not deterministic"
@@ -473,60 +483,6 @@ def test_gated_silu_fused(tdt, m, k, inter):
     assert st["max_rel"] <= 2 * TOL_MAX_REL, st     # two T roundings (GEMM, activation) against the oracle's pipeline
 
 
-@pytest.mark.parametrize("tdt", [torch.float16, torch.bfloat16])
-@pytest.mark.parametrize("m,k,inter", [(33, 512, 384), (64, 1024, 256), (130, 256, 640), (300, 1024, 1152), (513, 512, 128)])
-def test_gated_silu_fused_tcgen05(tdt, m, k, inter):
-    """the fused FFN activation beyond the streaming regime (M > 32): the 256-column whole-K tcgen05 tiles take the gate
-    half and the same columns of the up half as their two sub-tiles, so the epilogue thread of a TMEM lane holds gate
-    column j and up column j.  Against the oracle's two-step pipeline and against the activation of the SAME tile's plain
-    output (ragged token tiles, intermediate sizes that end inside a tile)."""
-    b = _b()
-    from cpmcu_b200 import capi as L
-    n = 2 * inter
-    dtype = mo.FP16 if tdt == torch.float16 else mo.BF16
-    prob = mo.make_problem(m, k, n, 128, dtype, seed=91 + m)
-    a, qw, sc = t_store(prob["a"], dtype), torch.from_numpy(prob["qweight"]).to(DEV), t_store(prob["scales_marlin"], dtype)
-    ws, c_tmp = scratch(m, n, k)
-    tile = 1001 if m > 128 else 1003          # what prefill_pick takes for gated launches
-    assert L.config_name(tile) in ("tc/bn256/bm256", "tc/bn256/bm128")
-    plain = b.gemm(a, qw, sc, ws, c_tmp, force_config=tile)
-    got = b.gemm(a, qw, sc, ws, c_tmp, gated_silu=True)
-    got2 = b.gemm(a, qw, sc, ws, c_tmp, gated_silu=True, pdl=True)
-    torch.cuda.synchronize()
-    assert got.shape == (m, inter) and torch.equal(got, got2)
-    g, u = plain[:, :inter].float(), plain[:, inter:].float()
-    want_own = (g * torch.sigmoid(g) * u)
-    d = (got.float() - want_own).abs()
-    ulp = 2.0 ** -10 if dtype == mo.FP16 else 2.0 ** -7
-    assert bool((d <= 1.5 * ulp * want_own.abs() + 1e-6).all()), float(d.max())
-    c, _ = mo.gemm(prob["a"], prob["qweight"], prob["scales_marlin"], k, n, 128, dtype)
-    want = mo.to_f32(mo.gated_silu_interleaved(c, dtype), dtype).astype(np.float64)
-    st = mo.error_stats(t_load(got, dtype), want, dtype)
-    # two T roundings (GEMM, activation) against the oracle's pipeline.  bf16: the metric divides the largest error by
-    # the MEAN |value| (~1); at the largest outputs (~16) half a bf16 ulp is already 0.06, so 300 x 1152 samples reach
-    # 2.5e-2 from rounding-boundary flips alone — the strict check is the one against the tile's own plain output above
-    assert st["max_rel"] <= (2 if dtype == mo.FP16 else 4) * TOL_MAX_REL, st
-
-
-def test_gated_silu_tcgen05_full_size():
-    """MiniCPM4-8B gate_up (4096 -> 2 x 16384) at a prefill chunk of 1024 tokens with the fused activation"""
-    b = _b()
-    m, k, inter = 1024, 4096, 16384
-    n = 2 * inter
-    g = torch.Generator(device=DEV).manual_seed(4)
-    qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=DEV, generator=g)
-    sc = (torch.rand((k // 128, n), device=DEV, generator=g) * 0.018 + 0.002).half()
-    a = (torch.randn((m, k), device=DEV, generator=g) * 0.1).half()
-    ws, c_tmp = scratch(m, n, k)
-    plain = b.gemm(a, qw, sc, ws, c_tmp, force_config=1001)
-    got = b.gemm(a, qw, sc, ws, c_tmp, gated_silu=True)
-    torch.cuda.synchronize()
-    gg, u = plain[:, :inter].float(), plain[:, inter:].float()
-    want = gg * torch.sigmoid(gg) * u
-    d = (got.float() - want).abs()
-    assert bool((d <= 1.5 * 2.0 ** -10 * want.abs() + 1e-6).all()), float(d.max())
-
-
 @pytest.mark.parametrize("m", [1, 16])
 def test_gated_silu_full_size(m):
     """MiniCPM4-8B gate_up (4096 -> 2 x 16384) with the fused activation, against the activation of the plain output"""
@@ -546,6 +502,8 @@ def test_gated_silu_full_size(m):
     d = (got.float() - want).abs()
     assert bool((d <= 1.5 * 2.0 ** -10 * want.abs() + 1e-6).all()), float(d.max())
     assert int(ws.abs().max()) == 0
+    with pytest.raises(ValueError):
+        b.gemm(torch.zeros((33, k), dtype=torch.float16, device=DEV), qw, sc, ws, c_tmp, gated_silu=True)
 
 
 @pytest.mark.parametrize("m,k,n", [(64, 16384, 4096), (64, 4096, 32768), (128, 16384, 4096)])

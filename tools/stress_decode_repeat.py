@@ -15,7 +15,10 @@ from cpmcu_b200 import capi as L  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--m", type=int, default=32)
 ap.add_argument("--passes", type=int, default=1000)
+ap.add_argument("--bf16", action="store_true")
+ap.add_argument("--gated", action="store_true", help="gate_up with the fused SiLU(gate) * up epilogue (compared with the first pass)")
 args = ap.parse_args()
+DT = torch.bfloat16 if args.bf16 else torch.float16
 DEV = "cuda"
 m = args.m
 shapes = [(4096, 4608), (4096, 4096), (4096, 32768), (16384, 4096)]
@@ -25,8 +28,8 @@ w = []
 for k, n in shapes:
     for _ in range(2):
         qw = torch.randint(-2**31, 2**31 - 1, (k // 16, 2 * n), dtype=torch.int32, device=DEV, generator=g)
-        sc = (torch.rand((k // 128, n), device=DEV, generator=g) * 0.018 + 0.002).half()
-        a = torch.randn((m, k), device=DEV, generator=g).half()
+        sc = (torch.rand((k // 128, n), device=DEV, generator=g) * 0.018 + 0.002).to(DT)
+        a = torch.randn((m, k), device=DEV, generator=g).to(DT)
         ws = torch.zeros(b.workspace_ints(n), dtype=torch.int32, device=DEV)
         ct = torch.empty(max(b.reduce_bytes_fast(m, n, k) // 4, 64), dtype=torch.float32, device=DEV)
         w.append((a, qw, sc, ws, ct))
