@@ -19,6 +19,9 @@
 // Tiles (nt, mt) are walked persistently, mt fastest, one CTA per SM; the accumulator is double
 // buffered in TMEM when it fits (<= 256 columns) so the epilogue overlaps the next tile.
 #pragma once
+#ifndef B200_NSUB2_SLACK
+#define B200_NSUB2_SLACK 0   // diagnosis of the withdrawn 256-column single-CTA tiles
+#endif
 #include "common.cuh"
 
 namespace b200 {
@@ -334,14 +337,14 @@ w4a16_prefill_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_cons
       for (int i = 0; i < Cfg::RPW; ++i)
         q[i] = lds128(sbase + Cfg::OFF_Q + sq * Cfg::Q_STAGE + q_lane + i * (Cfg::WPC * CHUNKS * 512));
       mbar_wait(bar_consumed + 8 * s, wph);  // W slot drained by the tensor core
-      if (PAIR) {
+      if (PAIR || (NSUB == 2 && B200_NSUB2_SLACK)) {
         // CTA pairs: one more k-block of slack.  The multicast commit that frees slot s arrives in BOTH CTAs at one
         // point in time while the two tensor cores do not finish reading their shared memory at the same instant; a
         // dequantiser that rewrites its W slot right behind that arrive corrupted a half-stage about once in 2700
         // launches (profiles/r02/o_pair_tile_race.txt; the TMA refill of the token slot is a microsecond later and
         // never showed it).  The UMMAs of a tensor core complete in order, so once the NEXT k-block's commit has
         // arrived this slot's reads are over on both SMs (two k-blocks: one left 1 mismatch in 32000 launches).
-        constexpr int kSlack = 2;
+        constexpr int kSlack = PAIR ? 2 : 1;
 #pragma unroll
         for (int d = 1; d <= kSlack; ++d) {
           const int it1 = it + d - STAGES;   // the d-th k-block after the one that last used slot s
