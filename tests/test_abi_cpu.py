@@ -73,3 +73,30 @@ def test_missing_library_fails_loudly(monkeypatch):
     monkeypatch.setenv("B200_W4A16_LIB", "/nonexistent/libb200_w4a16.so")
     with pytest.raises(capi.B200W4A16Error):
         capi.lib()
+
+
+def test_static_scratch_entry_point_rejects_sizes_beyond_its_maximum(lib):
+    """b200_w4a16_gemm_static_scratch checks M and N against the static array's limits before it touches CUDA, so the
+    rejection (value error + message) can be exercised without a GPU"""
+    import ctypes
+    null = ctypes.c_void_p(0)
+    assert lib.b200_w4a16_gemm_static_scratch(null, null, null, null, 33, 512, 1024, 128, 0, null) == 1
+    assert b"exceeds the maximum of 32" in lib.b200_w4a16_last_error()
+    assert lib.b200_w4a16_gemm_static_scratch(null, null, null, null, 1, 65536 + 64, 1024, 128, 0, null) == 1
+    assert b"exceeds the maximum of 65536" in lib.b200_w4a16_last_error()
+
+
+def test_configuration_names_of_the_kernel_families(lib):
+    """ids are stable within a build and every kernel family is reachable by name: the mma.sync streaming kernel, the
+    tensor-memory one (names ending in /tmem), the tcgen05 tiles incl. the CTA pair; the withdrawn tiles keep their ids"""
+    from cpmcu_b200 import capi
+    names = [capi.config_name(c) or "" for c in list(range(1, 200)) + list(range(1001, 1014))]
+    assert "__half/nt1/tn4x64/kb8x16/w8/s5/true" in names
+    assert "__nv_bfloat16/nt4/tn2x64/kb16x16/w8/s5/true/tmem" in names
+    assert "__half/nt2/tn4x64/kb8x16/w8/s5/false/tmem" in names
+    assert capi.config_name(1001) == "tc/bn256/bm256" and capi.config_name(1003) == "tc/bn256/bm128"
+    assert capi.config_name(1002) == "tc/bn128/bm256" and capi.config_name(1013) == "tc/pair256/bm256"
+    # what the heuristic takes for the decode widths (host-only planning: no GPU needed)
+    assert capi.config_name(capi.pick_config(1, 32768, 4096)) == "__half/nt1/tn4x64/kb8x16/w8/s5/true"
+    assert capi.config_name(capi.pick_config(16, 32768, 4096)) == "__half/nt2/tn2x64/kb16x16/w8/s5/true"
+    assert capi.config_name(capi.pick_config(24, 32768, 4096)) == "__half/nt4/tn2x64/kb16x16/w8/s5/true/tmem"
